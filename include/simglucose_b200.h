@@ -1,0 +1,178 @@
+/* simglucose_b200 -- C ABI of the B200-native batched patient simulator.
+ *
+ * The reference (Sawyerbatch/simglucose) is pure Python and has no FFI; its seams are Python
+ * objects.  Each entry point below names the reference interface it
+ * stands behind (paths relative to the reference root).  A reference-side binding is a ctypes
+ * stub; the in-tree one is simglucose_b200/_capi.py.
+ *
+ * Conventions
+ *   - plain C types only; every array argument is a DEVICE pointer unless its name ends in
+ *     _host; arrays over episodes are structure-of-arrays: element (i, e) of a [N][E] array
+ *     lives at ptr[i * n_episodes + e] so that one warp reads consecutive addresses;
+ *   - the caller owns every buffer it passes; the handle owns the resident episode state it
+ *     allocated in sg_create (nothing is allocated afterwards);
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous and stream-ordered;
+ *   - return value: SG_OK (0) or a negative sg_error; nothing throws across the ABI;
+ *   - one host thread per handle at a time.
+ */
+#ifndef SIMGLUCOSE_B200_H
+#define SIMGLUCOSE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SG_ABI_VERSION 1
+#define SG_NX 13          /* patient state size, t1dpatient.py:252 (params.iloc[2:15]) */
+
+/* The 32 columns of simglucose/params/vpatient_params.csv the hot path reads
+ * (T1DPatient.model t1dpatient.py:118-208; u2ss/BW by BBController
+ * controller/basal_bolus_ctrller.py:64; Vg by T1DPatient.observation t1dpatient.py:217-218). */
+typedef enum {
+    SG_P_BW = 0, SG_P_u2ss, SG_P_kmax, SG_P_kmin, SG_P_b, SG_P_d, SG_P_kabs, SG_P_f,
+    SG_P_kp1, SG_P_kp2, SG_P_kp3, SG_P_Fsnc, SG_P_ke1, SG_P_ke2, SG_P_k1, SG_P_k2,
+    SG_P_Vm0, SG_P_Vmx, SG_P_Km0, SG_P_m1, SG_P_m2, SG_P_m4, SG_P_m30, SG_P_ka1,
+    SG_P_ka2, SG_P_Vi, SG_P_p2u, SG_P_Ib, SG_P_ki, SG_P_kd, SG_P_ksc, SG_P_Vg,
+    SG_NPARAM
+} sg_param;
+
+typedef enum { SG_OK = 0, SG_ERR_ARG = -1, SG_ERR_CUDA = -2, SG_ERR_STATE = -3, SG_ERR_NOMEM = -4 } sg_error;
+
+/* sg_create flags */
+#define SG_FLAG_CARRY_H 1u   /* scipy 1.6.3 (Pipfile.lock) behaviour: the step size proposed at the end of one
+                                minute starts the next (WORK(7)=H); default 0 = scipy >= 1.7: HINIT every minute */
+#define SG_FLAG_FMA     2u   /* allow FMA contraction in the kernels (faster; not decision-identical to scipy) */
+
+/* Controller fused into sg_run. */
+typedef enum {
+    SG_CTRL_ACTIONS = 0,     /* per-step (basal, bolus) supplied by the caller: any Controller.policy
+                                (controller/base.py:11-34) evaluated outside */
+    SG_CTRL_BB = 1,          /* BBController._bb_policy, controller/basal_bolus_ctrller.py:64-80; ctrl = target, CR, CF */
+    SG_CTRL_PID = 2          /* PIDController.policy, controller/pid_ctrller.py:17-36; ctrl = P, I, D, target */
+} sg_controller;
+#define SG_NCTRL 4
+
+/* One history row per env-step: the columns of T1DSimEnv.show_history() (simulation/env.py:169-180)
+ * followed by the Step tuple fields (env.py:106-117) and the action that was applied. */
+typedef enum {
+    SG_T_BG = 0, SG_T_CGM, SG_T_CHO, SG_T_INSULIN, SG_T_LBGI, SG_T_HBGI, SG_T_RISK,
+    SG_T_OBS, SG_T_REWARD, SG_T_DONE, SG_T_BASAL, SG_T_BOLUS,
+    SG_NTRACE
+} sg_trace_col;
+
+/* Per-episode statistics accumulated over history rows (row 0 = reset row included). */
+typedef enum {
+    SG_S_ROWS = 0, SG_S_SUM_BG, SG_S_MIN_BG, SG_S_MAX_BG, SG_S_SUM_LBGI, SG_S_SUM_HBGI,
+    SG_S_SUM_RISK, SG_S_SUM_REWARD, SG_S_LT50, SG_S_LT70, SG_S_INRANGE, SG_S_GT180,
+    SG_S_GT250, SG_S_FIRST_DONE, SG_S_DOPRI_STEPS, SG_S_DOPRI_REJECTS,
+    SG_NSTAT
+} sg_stat;
+
+/* Sensor + pump rows (simglucose/params/sensor_params.csv, pump_params.csv) used by
+ * CGMSensor.measure (sensor/cgm.py:26-36) and InsulinPump.basal/.bolus (actuator/pump.py:23-39). */
+typedef struct {
+    int32_t sample_time;     /* minutes between CGM samples == minutes per env-step (env.py:75) */
+    double sensor_min, sensor_max;
+    double pump[6];          /* min_basal, max_basal, inc_basal, min_bolus, max_bolus, inc_bolus */
+} sg_hardware;
+
+typedef struct sg_context *sg_handle;
+
+/* Library / build identification; sg_version() == SG_ABI_VERSION. */
+int sg_version(void);
+const char *sg_last_error(void);
+
+/* Allocates the resident state for up to `capacity` episodes on CUDA device `device`.
+ * Stands where the reference builds one T1DSimEnv per patient (simulation/env.py:37-42,
+ * simulation/user_interface.py:364-372). */
+int sg_create(int device, int64_t capacity, uint32_t flags, sg_handle *out);
+int sg_destroy(sg_handle h);
+
+/* CGMSensor.withName / InsulinPump.withName (sensor/cgm.py:18-24, actuator/pump.py:16-21). */
+int sg_set_hardware(sg_handle h, const sg_hardware *hw_host);
+
+/* Parameter table: n_rows x SG_NPARAM (row-major, HOST) and the matching initial states
+ * n_rows x SG_NX (vpatient_params.csv columns x0_1..x0_13).  T1DPatient.withID/withName
+ * (patient/t1dpatient.py:44-68). */
+int sg_load_params(sg_handle h, const double *params_host, const double *x0_host, int32_t n_rows);
+
+/* T1DSimEnv.reset (simulation/env.py:119-155) for n_episodes episodes at once.
+ *   patient_row [E]            row of the table for each episode
+ *   params_soa  [SG_NPARAM][E] per-episode parameters (perturbed populations); NULL = use the table
+ *   x0          [SG_NX][E]     post-reset patient state (T1DPatient.reset t1dpatient.py:247-281,
+ *                              incl. random_init_bg); NULL = table x0
+ *   meal_minute [M][E] int32   episode minute of each announced meal in firing order, -1 = none
+ *   meal_grams  [M][E]         grams (scenario.get_action, simulation/scenario.py:33-42, scenario_gen.py:15-31)
+ *   noise       [n_noise][E]   CGM noise stream (sensor/noise_gen.py:61-69); the reset consumes 2 samples,
+ *                              every env-step one more
+ *   row0        [SG_NTRACE][E] history row 0 (may be NULL)
+ * The meal/noise/params buffers are BORROWED until the next sg_reset or sg_destroy. */
+int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const double *params_soa,
+             const double *x0, const int32_t *meal_minute, const double *meal_grams, int32_t max_meals,
+             const double *noise, int64_t n_noise, double *row0, void *stream);
+
+/* T1DSimEnv.step (simulation/env.py:66-117), lockstep over all episodes: one env-step of
+ * sample_time minutes with Action(basal[e], bolus[e]).  out [SG_NTRACE][E] = the new history row. */
+int sg_step(sg_handle h, const double *basal, const double *bolus, double *out, void *stream);
+
+/* SimObj.simulate (simulation/sim_engine.py:29-39) for every episode, n_steps env-steps fused in
+ * one launch with the controller evaluated on device.
+ *   ctrl_host [SG_NCTRL]      controller constants used for every episode when ctrl_rows is NULL
+ *   ctrl_rows [SG_NCTRL][E]   per-episode constants (BB: target, CR, CF from Quest.csv)
+ *   actions   [n_steps][2][E] (basal, bolus) when controller == SG_CTRL_ACTIONS
+ *   trace     [n_steps][SG_NTRACE][E] history rows 1..n_steps (may be NULL)
+ *   counters  [n_steps*sample_time][2][E] int32 (DOPRI5 steps, rejects) per minute (may be NULL) */
+int sg_run(sg_handle h, int32_t controller, const double *ctrl_host, const double *ctrl_rows,
+           const double *actions, int32_t n_steps, double *trace, int32_t *counters, void *stream);
+
+/* Resident state readers (T1DPatient.state t1dpatient.py:238-240; env histories). */
+int sg_get_state(sg_handle h, double *x_out /* [SG_NX][E] */, void *stream);
+int sg_get_stats(sg_handle h, double *stats_out /* [SG_NSTAT][E] */, void *stream);
+/* Per-episode solver status: 1 ok, -2 (more than 500 steps), -3 (step size too small): scipy's idid,
+ * checked by the reference through _odesolver.successful() (t1dpatient.py:112-116). */
+int sg_get_status(sg_handle h, int32_t *status_out /* [E] */, void *stream);
+
+/* Population aggregate of the per-episode statistics, reduced with warp shuffles then a fixed-order
+ * pass over per-block partials (deterministic): agg_out [SG_NSTAT] (sums; MIN_BG/MAX_BG extrema;
+ * FIRST_DONE = number of episodes that ever reported done). */
+int sg_reduce_stats(sg_handle h, double *agg_out, void *stream);
+
+int64_t sg_num_episodes(sg_handle h);
+/* Kernels launched through this handle since sg_create (bench.py's gpu_launches). */
+int64_t sg_launch_count(sg_handle h);
+
+/* ---- device-side generators of the per-episode input streams (distribution-compatible with the
+ * reference's numpy generators; counter-based Philox4x32-10 keyed by (seed, (episode_offset + e) / group_size): the episodes of
+ * one group -- e.g. the 30 patients simulated under one scenario/sensor seed -- share a stream) ---- */
+
+/* CGMNoise (sensor/noise_gen.py:15-97): out [n_noise][E].  W_dev [nsample][11] is the constant matrix of
+ * the cubic interp1d from eleven 15-minute knots to the sensor grid (nsample = floor(150/sample_time)+1,
+ * noise_gen.py:40-46); model_host = PACF, gamma, lambda, delta, xi (sensor_params.csv). */
+int sg_gen_noise(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsample, const double *W_dev,
+                 const double *model_host, uint64_t seed, int64_t episode_offset, int64_t group_size, void *stream);
+
+/* RandomScenario.create_scenario (simulation/scenario_gen.py:33-60), one schedule per calendar day, as a
+ * meal table meal_minute/meal_grams [max_meals][E] in firing order (-1 terminated). */
+int sg_gen_scenarios(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
+                     int32_t start_minute, int32_t horizon_minutes, uint64_t seed, int64_t episode_offset,
+                     int64_t group_size, void *stream);
+
+/* Perturbed population (BASELINE.json configs[3]): params_soa[i][e] = table[row[e]][i] * (1 + amplitude*u),
+ * u ~ U(-1, 1) i.i.d. per parameter.  table_dev: [n_rows][SG_NPARAM] on the device. */
+int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const int32_t *patient_row,
+                            int64_t n_episodes, double amplitude, uint64_t seed, int64_t episode_offset,
+                            void *stream);
+
+/* out[i] ~ U(lo, hi): random basal actions (BASELINE.json configs[2]). */
+int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, uint64_t offset, void *stream);
+
+/* FP64 pipe probe: n_blocks x n_threads threads each run `iters` x 8 independent DFMA; out gets one double per
+ * thread.  Flops = n_blocks * n_threads * iters * 16.  bench.py times it for the roofline denominator. */
+int sg_probe_dfma(double *out, int32_t n_blocks, int32_t n_threads, int64_t iters, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,176 @@
+"""TEST INFRASTRUCTURE ONLY -- generate tests/golden/*.npz by running the UNMODIFIED
+reference (through oracle/ref_harness.py) in the build container.
+
+    python oracle/make_golden.py [group ...]       # groups: see GROUPS below
+
+Every fixture records the inputs the batched engine consumes (patient row, x0, meal table,
+noise stream, controller spec / actions) and what the reference produced (history columns,
+observation / reward / done per step, per-minute DOPRI5 counters, final state).  The
+reference cannot travel to the GPU box; these files can.
+"""
+import os
+import sys
+from multiprocessing import Pool
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, _HERE)
+import ref_harness as H  # noqa: E402
+
+OUT = os.path.join(_HERE, '..', 'tests', 'golden')
+CUSTOM = [(7, 45), (12, 70), (16, 15), (18, 80), (23, 10)]   # tests/test_sim_engine.py:55
+
+
+def _pack(recs):
+    """list of per-episode dicts -> dict of stacked / object-free arrays."""
+    out = {}
+    keys = recs[0].keys()
+    n = len(recs)
+    for k in keys:
+        vals = [np.asarray(r[k]) for r in recs]
+        if k in ('meal_minute', 'meal_grams'):
+            m = max(1, max(v.size for v in vals))
+            fill = -1 if k == 'meal_minute' else 0.0
+            a = np.full((n, m), fill, dtype=vals[0].dtype)
+            for i, v in enumerate(vals):
+                a[i, :v.size] = v
+            out[k] = a
+        elif k == 'dop_counters':
+            out[k] = np.stack(vals).astype(np.int16)
+        else:
+            out[k] = np.stack(vals)
+    return out
+
+
+def _episode(job):
+    name, n_steps, kw = job
+    rec = H.run_episode(name, n_steps, **kw)
+    rec['controller_kind'] = np.array(kw.get('controller', ('bb', 140.0))[0])
+    c = list(kw.get('controller', ('bb', 140.0))[1:])
+    rec['controller_params'] = np.array(c + [0.0] * (4 - len(c)), dtype=np.float64)
+    return rec
+
+
+def _gym(job):
+    seed, n, name = job
+    rng = np.random.RandomState(seed + 7)
+    return H.run_gym(seed, n, rng.uniform(0.0, 0.05, size=n), patient_name=name)
+
+
+def _save(name, recs, **extra):
+    os.makedirs(OUT, exist_ok=True)
+    d = _pack(recs)
+    d.update(extra)
+    path = os.path.join(OUT, name + '.npz')
+    np.savez_compressed(path, **d)
+    print('wrote', os.path.normpath(path), '%.1f KB' % (os.path.getsize(path) / 1024.0), flush=True)
+
+
+def g_golden_config(pool):
+    """tests/test_sim_engine.py:87-113 (the config behind tests/sim_results.csv) + the file itself."""
+    import pandas as pd
+    recs = pool.map(_episode, [('adolescent#001', 960, dict(controller=('bb', 140.0), scenario=('random', 1),
+                                                            start_hour=0, sensor_seed=1))])
+    df = pd.read_csv(os.path.join(H.REFERENCE_ROOT, 'tests', 'sim_results.csv'))
+    cols = ['BG', 'CGM', 'CHO', 'insulin', 'LBGI', 'HBGI', 'Risk']
+    _save('golden_config', recs, sim_results_csv=df[cols].to_numpy(float), sim_results_cols=np.array(cols))
+
+
+def g_custom(pool):
+    """tests/test_sim_engine.py:55 CustomScenario, 1 day, BB (BASELINE.json configs[0])."""
+    jobs = [(n, 480, dict(controller=('bb', 140.0), scenario=('custom', CUSTOM), start_hour=0, sensor_seed=1))
+            for n in ('adolescent#001', 'adult#007', 'child#002')]
+    jobs.append(('adult#007', 480, dict(controller=('bb', 140.0), scenario=('custom', CUSTOM), start_hour=6,
+                                        sensor_seed=2)))
+    _save('custom_scenario', pool.map(_episode, jobs))
+
+
+def g_cohort_bb(pool):
+    """BASELINE.json configs[1]: all 30 patients x 3 days, RandomScenario seed 1, BBController."""
+    names = H.patient_names()
+    jobs = [(n, 1440, dict(controller=('bb', 140.0), scenario=('random', 1), start_hour=0, sensor_seed=1))
+            for n in names]
+    _save('cohort_bb_3day', pool.map(_episode, jobs))
+
+
+def g_cohort_pid(pool):
+    """BASELINE.json configs[4] subset: 30 patients x seeds 0..3, PID 1e-3/1e-5/1e-3 (examples/run_pid_controller.py:5), 1 day."""
+    names = H.patient_names()
+    jobs = [(n, 480, dict(controller=('pid', 1e-3, 1e-5, 1e-3, 140.0), scenario=('random', s), start_hour=0,
+                          sensor_seed=s)) for s in range(4) for n in names]
+    _save('cohort_pid_1day', pool.map(_episode, jobs))
+
+
+def g_open_loop(pool):
+    """Open-loop random basal actions (BASELINE.json configs[2] style), random_init_bg, odd start hours."""
+    names = H.patient_names()
+    jobs = []
+    for i, idx in enumerate([0, 4, 9, 10, 15, 19, 20, 24, 29, 7, 13, 27]):
+        rng = np.random.RandomState(100 + i)
+        acts = np.stack([rng.uniform(0.0, 0.05, 240), np.where(rng.rand(240) < 0.03, rng.uniform(0, 2.0, 240), 0.0)], 1)
+        jobs.append((names[idx], 240, dict(controller=('actions',), actions=acts, scenario=('random', 10 + i),
+                                           start_hour=(5 * i) % 24, sensor_seed=50 + i, random_init_bg=True,
+                                           patient_seed=200 + i)))
+    _save('open_loop_actions', pool.map(_episode, jobs))
+
+
+def g_hardware(pool):
+    """Other sensors / pump: GuardianRT (5 min), Navigator (1 min), Cozmo."""
+    jobs = [('adult#003', 144, dict(controller=('bb', 140.0), scenario=('random', 3), start_hour=6, sensor_seed=3,
+                                    sensor_name='GuardianRT', pump_name='Cozmo')),
+            ('child#006', 360, dict(controller=('bb', 140.0), scenario=('random', 4), start_hour=6, sensor_seed=4,
+                                    sensor_name='Navigator', pump_name='Insulet')),
+            ('adolescent#005', 144, dict(controller=('pid', 1e-3, 1e-5, 1e-3, 140.0), scenario=('random', 5),
+                                         start_hour=3, sensor_seed=5, sensor_name='GuardianRT', pump_name='Insulet'))]
+    recs = pool.map(_episode, jobs)
+    for r, j in zip(recs, jobs):
+        r['sensor_name'] = np.array(j[2]['sensor_name'])
+        r['pump_name'] = np.array(j[2]['pump_name'])
+    for i, r in enumerate(recs):
+        _save('hardware_%d' % i, [r])
+
+
+def g_gym(pool):
+    """gym wrapper: seeding chain known answers (tests/test_seed.py:19,23) and stepped outputs."""
+    jobs = [(0, 60, 'adolescent#001'), (1000, 60, 'adolescent#001'), (7, 60, 'adult#002'), (123, 60, 'child#009')]
+    _save('gym_seeded', pool.map(_gym, jobs))
+
+
+def g_noise(pool):
+    """CGMNoise streams (sensor/noise_gen.py) and RandomScenario schedules (scenario_gen.py) for generator parity."""
+    H._activate()
+    from datetime import datetime, timedelta
+    from simglucose.simulation.scenario_gen import RandomScenario
+    out = {}
+    for sname in ('Dexcom', 'GuardianRT', 'Navigator'):
+        out['noise_' + sname] = np.stack([H.noise_stream(sname, s, 400) for s in range(6)])
+    sched_min, sched_g = [], []
+    for s in range(8):
+        for hour in (0, 6):
+            start = datetime(2018, 1, 1, hour)
+            sc = RandomScenario(start_time=start, seed=s)
+            mm, gg = [], []
+            for m in range(3 * 1440):
+                a = sc.get_action(start + timedelta(minutes=m))
+                if a.meal != 0:
+                    mm.append(m); gg.append(float(a.meal))
+            mm = (mm + [-1] * 24)[:24]; gg = (gg + [0.0] * 24)[:24]
+            sched_min.append(mm); sched_g.append(gg)
+    out['sched_seed_hour'] = np.array([(s, h) for s in range(8) for h in (0, 6)], dtype=np.int32)
+    out['sched_minute'] = np.array(sched_min, dtype=np.int32)
+    out['sched_grams'] = np.array(sched_g, dtype=np.float64)
+    os.makedirs(OUT, exist_ok=True)
+    path = os.path.join(OUT, 'generators.npz')
+    np.savez_compressed(path, **out)
+    print('wrote', os.path.normpath(path), flush=True)
+
+
+GROUPS = dict(golden_config=g_golden_config, custom=g_custom, cohort_bb=g_cohort_bb, cohort_pid=g_cohort_pid,
+              open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise)
+
+if __name__ == '__main__':
+    groups = sys.argv[1:] or list(GROUPS)
+    with Pool(int(os.environ.get('GOLDEN_PROCS', os.cpu_count() or 1))) as pool:
+        for g in groups:
+            GROUPS[g](pool)

@@ -1,0 +1,92 @@
+"""ctypes binding of include/simglucose_b200.h (the C-ABI of the CUDA library).
+
+There is no CPU fallback: if the shared library is missing or does not load, importing a symbol from
+it raises.  `load()` never builds anything; run `python -m simglucose_b200.build` (or
+`__graft_entry__.build()`) first.
+"""
+import ctypes as C
+import os
+
+from .build import LIB_PATH
+
+SG_ABI_VERSION = 1
+NX = 13
+NPARAM = 32
+NTRACE = 12
+NSTAT = 16
+NCTRL = 4
+
+PARAMS = ['BW', 'u2ss', 'kmax', 'kmin', 'b', 'd', 'kabs', 'f', 'kp1', 'kp2', 'kp3', 'Fsnc', 'ke1', 'ke2',
+          'k1', 'k2', 'Vm0', 'Vmx', 'Km0', 'm1', 'm2', 'm4', 'm30', 'ka1', 'ka2', 'Vi', 'p2u', 'Ib', 'ki',
+          'kd', 'ksc', 'Vg']
+TRACE_COLS = ['BG', 'CGM', 'CHO', 'insulin', 'LBGI', 'HBGI', 'Risk', 'obs', 'reward', 'done', 'basal', 'bolus']
+STAT_COLS = ['rows', 'sum_bg', 'min_bg', 'max_bg', 'sum_lbgi', 'sum_hbgi', 'sum_risk', 'sum_reward', 'lt50',
+             'lt70', 'inrange', 'gt180', 'gt250', 'first_done', 'dopri_steps', 'dopri_rejects']
+CTRL_ACTIONS, CTRL_BB, CTRL_PID = 0, 1, 2
+FLAG_CARRY_H, FLAG_FMA = 1, 2
+
+# every symbol include/simglucose_b200.h declares
+SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_hardware', 'sg_load_params',
+           'sg_reset', 'sg_step', 'sg_run', 'sg_get_state', 'sg_get_stats', 'sg_get_status',
+           'sg_reduce_stats', 'sg_num_episodes', 'sg_launch_count',
+           'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma']
+
+
+class Hardware(C.Structure):
+    _fields_ = [('sample_time', C.c_int32), ('sensor_min', C.c_double), ('sensor_max', C.c_double),
+                ('pump', C.c_double * 6)]
+
+
+class SgError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree CUDA library and declare the prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SgError('CUDA library %s is missing: run `python -m simglucose_b200.build` '
+                      '(there is no CPU fallback)' % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, dp, ip = C.c_void_p, C.c_void_p, C.c_void_p      # device pointers travel as integers
+    L.sg_version.restype = C.c_int
+    L.sg_last_error.restype = C.c_char_p
+    L.sg_create.argtypes = [C.c_int, C.c_int64, C.c_uint32, C.POINTER(C.c_void_p)]
+    L.sg_destroy.argtypes = [vp]
+    L.sg_set_hardware.argtypes = [vp, C.POINTER(Hardware)]
+    L.sg_load_params.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int32]
+    L.sg_reset.argtypes = [vp, C.c_int64, ip, dp, dp, ip, dp, C.c_int32, dp, C.c_int64, dp, vp]
+    L.sg_step.argtypes = [vp, dp, dp, dp, vp]
+    L.sg_run.argtypes = [vp, C.c_int32, C.POINTER(C.c_double), dp, dp, C.c_int32, dp, ip, vp]
+    L.sg_get_state.argtypes = [vp, dp, vp]
+    L.sg_get_stats.argtypes = [vp, dp, vp]
+    L.sg_get_status.argtypes = [vp, ip, vp]
+    L.sg_reduce_stats.argtypes = [vp, dp, vp]
+    L.sg_num_episodes.argtypes = [vp]
+    L.sg_num_episodes.restype = C.c_int64
+    L.sg_launch_count.argtypes = [vp]
+    L.sg_launch_count.restype = C.c_int64
+    if True:
+        L.sg_gen_noise.argtypes = [dp, C.c_int64, C.c_int64, C.c_int32, dp, C.POINTER(C.c_double), C.c_uint64, C.c_int64, C.c_int64, vp]
+        L.sg_gen_scenarios.argtypes = [ip, dp, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_uint64, C.c_int64, C.c_int64, vp]
+        L.sg_gen_perturbed_params.argtypes = [dp, dp, ip, C.c_int64, C.c_double, C.c_uint64, C.c_int64, vp]
+        L.sg_probe_dfma.argtypes = [dp, C.c_int32, C.c_int32, C.c_int64, vp]
+        L.sg_gen_uniform.argtypes = [dp, C.c_int64, C.c_double, C.c_double, C.c_uint64, C.c_uint64, vp]
+    for name in SYMBOLS:
+        f = getattr(L, name, None)
+        if f is not None and f.restype is C.c_int and name != 'sg_version':
+            f.restype = C.c_int
+    if L.sg_version() != SG_ABI_VERSION:
+        raise SgError('ABI version mismatch: library %d, binding %d' % (L.sg_version(), SG_ABI_VERSION))
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise SgError('simglucose_b200 C-ABI error %d: %s' % (rc, load().sg_last_error().decode()))

@@ -1,0 +1,267 @@
+// C-ABI of the batched simulator (include/simglucose_b200.h).  Host-side bookkeeping only: argument
+// checks, the resident state allocation, and kernel launches on the caller's stream.
+#include "../../include/simglucose_b200.h"
+#include "sg_kernels.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+static_assert(SG_NTRACE == sgk::NTRACE, "trace columns");
+static_assert(SG_NSTAT == sgk::NSTAT, "stat columns");
+static_assert(SG_NCTRL == sgk::NCTRL, "controller constants");
+
+namespace {
+
+thread_local char g_err[256] = "";
+
+int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
+{
+    if (ce != cudaSuccess) snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(ce));
+    else snprintf(g_err, sizeof g_err, "%s", what);
+    return code;
+}
+
+}  // namespace
+
+struct sg_context {
+    int device = 0;
+    int64_t cap = 0, n = 0;
+    uint32_t flags = 0;
+    sgk::Hardware hw{};
+    bool have_hw = false;
+    double *sd = nullptr;
+    int32_t *si = nullptr;
+    double *stats = nullptr;
+    double *table = nullptr, *table_x0 = nullptr;
+    int32_t n_rows = 0;
+    double *partials = nullptr;
+    int32_t max_partials = 0;
+    // borrowed from the last sg_reset
+    const int32_t *patient_row = nullptr;
+    const double *params_soa = nullptr;
+    const int32_t *meal_minute = nullptr;
+    const double *meal_grams = nullptr;
+    int32_t max_meals = 0;
+    const double *noise = nullptr;
+    int64_t n_noise = 0;
+    int64_t steps_done = 0;
+    bool is_reset = false;
+    int64_t launches = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+sgk::EpisodeArgs base_args(const sg_context *h)
+{
+    sgk::EpisodeArgs a{};
+    a.n = h->n; a.cap = h->cap;
+    a.sd = h->sd; a.si = h->si; a.stats = h->stats;
+    a.params_soa = h->params_soa; a.table = h->table; a.table_x0 = h->table_x0;
+    a.patient_row = h->patient_row;
+    a.meal_minute = h->meal_minute; a.meal_grams = h->meal_grams; a.max_meals = h->max_meals;
+    a.noise = h->noise; a.n_noise = h->n_noise;
+    a.hw = h->hw;
+    a.carry_h = (h->flags & SG_FLAG_CARRY_H) ? 1 : 0;
+    return a;
+}
+
+bool use_fma(const sg_context *h) { return (h->flags & SG_FLAG_FMA) != 0; }
+
+}  // namespace
+
+extern "C" {
+
+int sg_version(void) { return SG_ABI_VERSION; }
+const char *sg_last_error(void) { return g_err; }
+
+int sg_create(int device, int64_t capacity, uint32_t flags, sg_handle *out)
+{
+    if (!out || capacity <= 0) return fail(SG_ERR_ARG, "sg_create: bad arguments");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev <= 0) return fail(SG_ERR_CUDA, "sg_create: no CUDA device", ce);
+    if (device < 0 || device >= ndev) return fail(SG_ERR_ARG, "sg_create: device out of range");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(SG_ERR_CUDA, "sg_create: cudaSetDevice failed");
+    sg_context *h = new (std::nothrow) sg_context();
+    if (!h) return fail(SG_ERR_NOMEM, "sg_create: host allocation failed");
+    h->device = device; h->cap = capacity; h->flags = flags;
+    h->max_partials = sg_strict::reduce_blocks(capacity);
+    ce = cudaMalloc(&h->sd, sizeof(double) * sgk::SD_COUNT * capacity);
+    if (ce == cudaSuccess) ce = cudaMalloc(&h->si, sizeof(int32_t) * sgk::SI_COUNT * capacity);
+    if (ce == cudaSuccess) ce = cudaMalloc(&h->stats, sizeof(double) * sgk::NSTAT * capacity);
+    if (ce == cudaSuccess) ce = cudaMalloc(&h->partials, sizeof(double) * sgk::NSTAT * h->max_partials);
+    if (ce != cudaSuccess) {
+        sg_destroy(h);
+        return fail(SG_ERR_NOMEM, "sg_create: cudaMalloc", ce);
+    }
+    *out = h;
+    return SG_OK;
+}
+
+int sg_destroy(sg_handle h)
+{
+    if (!h) return SG_OK;
+    DeviceGuard g(h->device);
+    cudaFree(h->sd); cudaFree(h->si); cudaFree(h->stats); cudaFree(h->partials);
+    cudaFree(h->table); cudaFree(h->table_x0);
+    delete h;
+    return SG_OK;
+}
+
+int sg_set_hardware(sg_handle h, const sg_hardware *hw)
+{
+    if (!h || !hw) return fail(SG_ERR_ARG, "sg_set_hardware: null argument");
+    if (hw->sample_time < 1 || !(hw->pump[2] > 0.0) || !(hw->pump[5] > 0.0))
+        return fail(SG_ERR_ARG, "sg_set_hardware: sample_time >= 1 and pump increments > 0 required");
+    h->hw.st = hw->sample_time;
+    h->hw.smin = hw->sensor_min; h->hw.smax = hw->sensor_max;
+    memcpy(h->hw.pump, hw->pump, sizeof h->hw.pump);
+    h->have_hw = true;
+    return SG_OK;
+}
+
+int sg_load_params(sg_handle h, const double *params_host, const double *x0_host, int32_t n_rows)
+{
+    if (!h || !params_host || !x0_host || n_rows <= 0) return fail(SG_ERR_ARG, "sg_load_params: bad arguments");
+    DeviceGuard g(h->device);
+    cudaFree(h->table); cudaFree(h->table_x0);
+    h->table = h->table_x0 = nullptr; h->n_rows = 0;
+    cudaError_t ce = cudaMalloc(&h->table, sizeof(double) * SG_NPARAM * n_rows);
+    if (ce == cudaSuccess) ce = cudaMalloc(&h->table_x0, sizeof(double) * SG_NX * n_rows);
+    if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_load_params: cudaMalloc", ce);
+    ce = cudaMemcpy(h->table, params_host, sizeof(double) * SG_NPARAM * n_rows, cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess)
+        ce = cudaMemcpy(h->table_x0, x0_host, sizeof(double) * SG_NX * n_rows, cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_load_params: cudaMemcpy", ce);
+    h->n_rows = n_rows;
+    return SG_OK;
+}
+
+int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const double *params_soa,
+             const double *x0, const int32_t *meal_minute, const double *meal_grams, int32_t max_meals,
+             const double *noise, int64_t n_noise, double *row0, void *stream)
+{
+    if (!h) return fail(SG_ERR_ARG, "sg_reset: null handle");
+    if (!h->have_hw) return fail(SG_ERR_STATE, "sg_reset: call sg_set_hardware first");
+    if (n_episodes <= 0 || n_episodes > h->cap) return fail(SG_ERR_ARG, "sg_reset: n_episodes outside 1..capacity");
+    if (!params_soa && (!patient_row || !h->table)) return fail(SG_ERR_ARG, "sg_reset: need params_soa, or patient_row + sg_load_params");
+    if (!x0 && (!patient_row || !h->table_x0)) return fail(SG_ERR_ARG, "sg_reset: need x0, or patient_row + sg_load_params");
+    if (max_meals < 0 || (max_meals > 0 && (!meal_minute || !meal_grams))) return fail(SG_ERR_ARG, "sg_reset: meal table");
+    if (!noise || n_noise < 2) return fail(SG_ERR_ARG, "sg_reset: the reset consumes two noise samples");
+    DeviceGuard g(h->device);
+    h->n = n_episodes;
+    h->patient_row = patient_row; h->params_soa = params_soa;
+    h->meal_minute = meal_minute; h->meal_grams = meal_grams; h->max_meals = max_meals;
+    h->noise = noise; h->n_noise = n_noise;
+    h->steps_done = 0;
+    sgk::EpisodeArgs a = base_args(h);
+    a.x0 = x0; a.row0 = row0;
+    cudaError_t ce = use_fma(h) ? sg_fma::launch_reset(a, (cudaStream_t)stream)
+                                : sg_strict::launch_reset(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_reset: launch", ce);
+    h->launches++;
+    h->is_reset = true;
+    return SG_OK;
+}
+
+static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, const double *ctrl_rows,
+                    const double *basal, const double *bolus, int64_t act_stride, int32_t n_steps,
+                    double *trace, int32_t *counters, void *stream, const char *who)
+{
+    if (!h->is_reset) return fail(SG_ERR_STATE, who);
+    if (h->steps_done + n_steps + 2 > h->n_noise) return fail(SG_ERR_ARG, "noise stream too short for the requested steps");
+    if (n_steps == 0) return SG_OK;
+    DeviceGuard g(h->device);
+    sgk::EpisodeArgs a = base_args(h);
+    a.controller = controller;
+    if (ctrl_host) memcpy(a.ctrl, ctrl_host, sizeof a.ctrl);
+    a.ctrl_rows = ctrl_rows;
+    a.act_basal = basal; a.act_bolus = bolus; a.act_stride = act_stride;
+    a.n_steps = n_steps;
+    a.trace = trace; a.counters = counters;
+    cudaError_t ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream)
+                                : sg_strict::launch_run(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
+    h->launches++;
+    h->steps_done += n_steps;
+    return SG_OK;
+}
+
+int sg_run(sg_handle h, int32_t controller, const double *ctrl_host, const double *ctrl_rows,
+           const double *actions, int32_t n_steps, double *trace, int32_t *counters, void *stream)
+{
+    if (!h) return fail(SG_ERR_ARG, "sg_run: null handle");
+    if (n_steps < 0) return fail(SG_ERR_ARG, "sg_run: n_steps < 0");
+    if (controller < SG_CTRL_ACTIONS || controller > SG_CTRL_PID) return fail(SG_ERR_ARG, "sg_run: unknown controller");
+    if (controller == SG_CTRL_ACTIONS && !actions) return fail(SG_ERR_ARG, "sg_run: actions required");
+    if (controller != SG_CTRL_ACTIONS && !ctrl_host && !ctrl_rows) return fail(SG_ERR_ARG, "sg_run: controller constants required");
+    return run_impl(h, controller, ctrl_host, ctrl_rows, actions, actions ? actions + h->n : nullptr, 2 * h->n,
+                    n_steps, trace, counters, stream, "sg_run");
+}
+
+int sg_step(sg_handle h, const double *basal, const double *bolus, double *out, void *stream)
+{
+    if (!h) return fail(SG_ERR_ARG, "sg_step: null handle");
+    if (!basal || !bolus) return fail(SG_ERR_ARG, "sg_step: basal and bolus required");
+    return run_impl(h, SG_CTRL_ACTIONS, nullptr, nullptr, basal, bolus, 0, 1, out, nullptr, stream, "sg_step");
+}
+
+static int copy_out(sg_handle h, void *dst, const void *src, size_t elem, int rows, void *stream, const char *who)
+{
+    if (!h || !dst) return fail(SG_ERR_ARG, who);
+    if (!h->is_reset) return fail(SG_ERR_STATE, who);
+    DeviceGuard g(h->device);
+    cudaError_t ce = cudaMemcpy2DAsync(dst, elem * h->n, src, elem * h->cap, elem * h->n, rows,
+                                       cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
+    return SG_OK;
+}
+
+int sg_get_state(sg_handle h, double *x_out, void *stream)
+{
+    return copy_out(h, x_out, h ? h->sd : nullptr, sizeof(double), SG_NX, stream, "sg_get_state");
+}
+
+int sg_get_stats(sg_handle h, double *stats_out, void *stream)
+{
+    return copy_out(h, stats_out, h ? h->stats : nullptr, sizeof(double), SG_NSTAT, stream, "sg_get_stats");
+}
+
+int sg_get_status(sg_handle h, int32_t *status_out, void *stream)
+{
+    return copy_out(h, status_out, h ? h->si + (int64_t)sgk::SI_STATUS * h->cap : nullptr, sizeof(int32_t), 1,
+                    stream, "sg_get_status");
+}
+
+int sg_reduce_stats(sg_handle h, double *agg_out, void *stream)
+{
+    if (!h || !agg_out) return fail(SG_ERR_ARG, "sg_reduce_stats: null argument");
+    if (!h->is_reset) return fail(SG_ERR_STATE, "sg_reduce_stats: call sg_reset first");
+    DeviceGuard g(h->device);
+    sgk::ReduceArgs r{};
+    r.n = h->n; r.cap = h->cap; r.stats = h->stats; r.partials = h->partials; r.out = agg_out;
+    r.n_blocks = sg_strict::reduce_blocks(h->n);
+    cudaError_t ce = sg_strict::launch_reduce(r, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_reduce_stats: launch", ce);
+    h->launches += 2;
+    return SG_OK;
+}
+
+int64_t sg_num_episodes(sg_handle h) { return h ? h->n : 0; }
+int64_t sg_launch_count(sg_handle h) { return h ? h->launches : 0; }
+
+}  // extern "C"

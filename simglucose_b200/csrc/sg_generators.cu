@@ -1,0 +1,236 @@
+// Device-side generators of the per-episode INPUT streams.
+//
+// The reference draws these from numpy's MT19937 one Python call at a time:
+//   CGM noise       CGMNoise / noise15_iter            simglucose/sensor/noise_gen.py:15-97
+//   meal schedules  RandomScenario.create_scenario     simglucose/simulation/scenario_gen.py:33-60
+//   parameter jitter (BASELINE.json configs[3]: +-10 % per used parameter)
+// For seeds that must replay the reference bit for bit the host generators in
+// simglucose_b200/streams.py are used instead; the kernels here produce the same DISTRIBUTIONS from a
+// counter-based Philox4x32-10 stream (key = seed, counter = (global episode index, draw index)), so
+// any shard of a population can be generated independently on any GPU.
+#include "../../include/simglucose_b200.h"
+
+#include <cmath>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace {
+
+struct Philox {
+    uint32_t key[2];
+    uint32_t ctr[4];
+    uint32_t out[4];
+    int have;
+
+    __device__ Philox(uint64_t seed, uint64_t stream, uint32_t substream)
+    {
+        key[0] = (uint32_t)seed; key[1] = (uint32_t)(seed >> 32);
+        ctr[0] = 0; ctr[1] = substream; ctr[2] = (uint32_t)stream; ctr[3] = (uint32_t)(stream >> 32);
+        have = 0;
+    }
+    __device__ void round(uint32_t (&c)[4], const uint32_t (&k)[2])
+    {
+        const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+        const uint32_t hi0 = __umulhi(M0, c[0]), lo0 = M0 * c[0];
+        const uint32_t hi1 = __umulhi(M1, c[2]), lo1 = M1 * c[2];
+        const uint32_t n0 = hi1 ^ c[1] ^ k[0], n1 = lo1, n2 = hi0 ^ c[3] ^ k[1], n3 = lo0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    }
+    __device__ void refill()
+    {
+        uint32_t c[4] = {ctr[0], ctr[1], ctr[2], ctr[3]};
+        uint32_t k[2] = {key[0], key[1]};
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            round(c, k);
+            k[0] += 0x9E3779B9u; k[1] += 0xBB67AE85u;
+        }
+        out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+        ctr[0]++;
+        have = 4;
+    }
+    __device__ uint32_t next32()
+    {
+        if (have == 0) refill();
+        return out[--have];
+    }
+    // uniform in (0, 1), 53 bits
+    __device__ double uniform()
+    {
+        const uint64_t a = next32(), b = next32();
+        const uint64_t bits = ((a << 32) | b) >> 11;
+        return ((double)bits + 0.5) * (1.0 / 9007199254740992.0);
+    }
+    __device__ double normal()
+    {
+        // inverse-CDF normal: one uniform per draw, monotone, no rejection
+        return normcdfinv(uniform());
+    }
+};
+
+constexpr int MAX_W = 151 * 11;   // Navigator: 151 samples per window
+
+// CGMNoise: AR(1)-type chain at 15-minute knots, Johnson SU transform, cubic interpolation to the
+// sensor grid expressed as a constant matrix W [(nsample) x 11] (row 0 = the carried knot, dropped).
+__global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
+                                                   const double *W, double pacf, double gamma, double lambda,
+                                                   double delta, double xi, uint64_t seed, int64_t ep0, int64_t group)
+{
+    extern __shared__ double sW[];
+    for (int i = threadIdx.x; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
+    __syncthreads();
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    Philox rng(seed, (uint64_t)((ep0 + e) / group), 0x6e6f6973u /* 'nois' */);
+    double ar = rng.normal();                                   // noise_gen.py:84-85
+    double knots[11];
+    knots[10] = xi + lambda * sinh((ar - gamma) / delta);       // _noise_init, noise_gen.py:24
+    int64_t pos = 0;
+    while (pos < n_noise) {
+        knots[0] = knots[10];                                   // noise_gen.py:33-36
+#pragma unroll
+        for (int k = 1; k <= 10; k++) {
+            ar = pacf * (ar + rng.normal());                    // noise_gen.py:86-88
+            knots[k] = xi + lambda * sinh((ar - gamma) / delta);
+        }
+        for (int r = 1; r < nsample && pos < n_noise; r++, pos++) {   // noise[1:], noise_gen.py:47
+            double v = 0.0;
+#pragma unroll
+            for (int k = 0; k < 11; k++) v += sW[r * 11 + k] * knots[k];
+            out[pos * n + e] = v;
+        }
+    }
+}
+
+// RandomScenario: one schedule per calendar day, six candidate meals (scenario_gen.py:38-58).
+__global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, double *meal_grams, int64_t n,
+                                                      int max_meals, int start_minute, int horizon,
+                                                      uint64_t seed, int64_t ep0, int64_t group)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const double prob[6] = {0.95, 0.3, 0.95, 0.3, 0.95, 0.3};
+    const double lb[6] = {300, 540, 600, 840, 960, 1200}, ub[6] = {540, 600, 840, 960, 1200, 1380};
+    const double mu[6] = {420, 570, 720, 900, 1080, 1290}, sd[6] = {60, 30, 60, 30, 60, 30};
+    const double amu[6] = {45, 10, 70, 10, 80, 10}, asd[6] = {10, 5, 10, 5, 10, 5};
+    Philox rng(seed, (uint64_t)((ep0 + e) / group), 0x6d65616cu /* 'meal' */);
+    int pos = 0, last = -1;
+    const int n_days = (start_minute + horizon + 1439) / 1440;
+    for (int day = 0; day < n_days; day++) {
+        for (int i = 0; i < 6; i++) {
+            const double u = rng.uniform(), ut = rng.uniform(), za = rng.normal();
+            if (!(u < prob[i])) continue;
+            const double Fa = normcdf((lb[i] - mu[i]) / sd[i]), Fb = normcdf((ub[i] - mu[i]) / sd[i]);
+            double t = mu[i] + sd[i] * normcdfinv(Fa + ut * (Fb - Fa));
+            t = fmin(fmax(t, lb[i]), ub[i]);
+            const int tmin = (int)rint(t);                               // np.round
+            const double grams = fmax(rint(amu[i] + asd[i] * za), 0.0);  // max(round(normal), 0)
+            const int m = day * 1440 + tmin - start_minute;              // episode minute
+            if (m < 0 || m >= horizon || m <= last) continue;            // duplicates: first wins (list.index)
+            if (grams == 0.0) { last = m; continue; }                    // Action(meal=0) is "no meal" (get_action)
+            if (pos < max_meals) {
+                meal_minute[(int64_t)pos * n + e] = m;
+                meal_grams[(int64_t)pos * n + e] = grams;
+                pos++; last = m;
+            }
+        }
+    }
+    for (; pos < max_meals; pos++) {
+        meal_minute[(int64_t)pos * n + e] = -1;
+        meal_grams[(int64_t)pos * n + e] = 0.0;
+    }
+}
+
+// params_soa[i][e] = table[row[e]][i] * (1 + amp * u), u ~ U(-1, 1) i.i.d. per parameter.
+__global__ void __launch_bounds__(128) perturb_kernel(double *params_soa, const double *table, const int32_t *row,
+                                                     int64_t n, double amp, uint64_t seed, int64_t ep0, int64_t group)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    Philox rng(seed, (uint64_t)((ep0 + e) / group), 0x70617261u /* 'para' */);
+    const double *t = table + (int64_t)row[e] * SG_NPARAM;
+#pragma unroll 4
+    for (int i = 0; i < SG_NPARAM; i++) {
+        const double u = 2.0 * rng.uniform() - 1.0;
+        params_soa[(int64_t)i * n + e] = t[i] * (1.0 + amp * u);
+    }
+}
+
+__global__ void __launch_bounds__(256) uniform_kernel(double *out, int64_t n, double lo, double hi, uint64_t seed,
+                                                     uint64_t offset)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Philox rng(seed, offset + (uint64_t)i, 0x756e6966u /* 'unif' */);
+    out[i] = lo + (hi - lo) * rng.uniform();
+}
+
+inline unsigned blocks(int64_t n, int b) { return (unsigned)((n + b - 1) / b); }
+
+}  // namespace
+
+extern "C" {
+
+int sg_gen_noise(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsample, const double *W_dev,
+                 const double *model_host, uint64_t seed, int64_t episode_offset, int64_t group_size, void *stream)
+{
+    if (!out || !W_dev || !model_host || n_episodes <= 0 || n_noise <= 0 || nsample < 2 || nsample * 11 > MAX_W ||
+        group_size < 1)
+        return SG_ERR_ARG;
+    noise_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+        out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
+        model_host[4], seed, episode_offset, group_size);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_scenarios(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
+                     int32_t start_minute, int32_t horizon_minutes, uint64_t seed, int64_t episode_offset,
+                     int64_t group_size, void *stream)
+{
+    if (!meal_minute || !meal_grams || n_episodes <= 0 || max_meals <= 0 || start_minute < 0 ||
+        start_minute >= 1440 || horizon_minutes <= 0 || group_size < 1)
+        return SG_ERR_ARG;
+    scenario_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
+        meal_minute, meal_grams, n_episodes, max_meals, start_minute, horizon_minutes, seed, episode_offset, group_size);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const int32_t *patient_row,
+                            int64_t n_episodes, double amplitude, uint64_t seed, int64_t episode_offset,
+                            void *stream)
+{
+    if (!params_soa || !table_dev || !patient_row || n_episodes <= 0) return SG_ERR_ARG;
+    perturb_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
+        params_soa, table_dev, patient_row, n_episodes, amplitude, seed, episode_offset, 1);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, uint64_t offset, void *stream)
+{
+    if (!out || n <= 0) return SG_ERR_ARG;
+    uniform_kernel<<<blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(out, n, lo, hi, seed, offset);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+}  // extern "C"
+
+// ---- FP64 pipe probe: the measured DFMA peak bench.py uses as the roofline denominator ----------
+namespace {
+__global__ void __launch_bounds__(256) dfma_probe_kernel(double *out, int64_t iters)
+{
+    const double a = 1.0 + 1e-9 * threadIdx.x, b = 1e-12;
+    double v0 = 1.0, v1 = 1.1, v2 = 1.2, v3 = 1.3, v4 = 1.4, v5 = 1.5, v6 = 1.6, v7 = 1.7;
+    for (int64_t i = 0; i < iters; i++) {
+        v0 = fma(v0, a, b); v1 = fma(v1, a, b); v2 = fma(v2, a, b); v3 = fma(v3, a, b);
+        v4 = fma(v4, a, b); v5 = fma(v5, a, b); v6 = fma(v6, a, b); v7 = fma(v7, a, b);
+    }
+    out[(int64_t)blockIdx.x * blockDim.x + threadIdx.x] = ((v0 + v1) + (v2 + v3)) + ((v4 + v5) + (v6 + v7));
+}
+}  // namespace
+
+extern "C" int sg_probe_dfma(double *out, int32_t n_blocks, int32_t n_threads, int64_t iters, void *stream)
+{
+    if (!out || n_blocks <= 0 || n_threads <= 0 || n_threads > 256 || iters <= 0) return SG_ERR_ARG;
+    dfma_probe_kernel<<<n_blocks, n_threads, 0, (cudaStream_t)stream>>>(out, iters);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}

@@ -1,0 +1,337 @@
+// Kernels of the batched closed-loop simulator.  Compiled twice (see build.py):
+//   -fmad=false -DSG_NS=sg_strict   decision-faithful arithmetic (default mode)
+//   -fmad=true  -DSG_NS=sg_fma      FMA contraction allowed (SG_FLAG_FMA)
+//
+// reset_kernel  T1DSimEnv.reset                      simulation/env.py:119-155
+// run_kernel    SimObj.simulate / T1DSimEnv.step     simulation/sim_engine.py:29-39, env.py:48-117
+//               with BBController / PIDController    controller/basal_bolus_ctrller.py:64-80,
+//                                                    controller/pid_ctrller.py:17-36
+// reduce_*      population statistics (warp shuffles -> block partials -> fixed-order pass)
+#include "sg_kernels.cuh"
+#include "sg_model.cuh"
+
+#ifndef SG_NS
+#error "compile with -DSG_NS=sg_strict or -DSG_NS=sg_fma"
+#endif
+
+namespace SG_NS {
+using namespace sgk;
+
+struct ParamLoad {
+    const double *base;
+    int64_t stride;
+    __device__ __forceinline__ double operator()(int i) const { return __ldg(base + i * stride); }
+};
+
+__device__ __forceinline__ ParamLoad param_source(const EpisodeArgs &a, int64_t e)
+{
+    if (a.params_soa) return ParamLoad{a.params_soa + e, a.n};
+    return ParamLoad{a.table + (int64_t)a.patient_row[e] * P_COUNT, 1};
+}
+
+// CGMSensor.measure at a sampling minute, cgm.py:28-33.
+__device__ __forceinline__ double cgm_sample(const EpisodeArgs &a, int64_t e, double bg, int &noise_pos)
+{
+    double cgm = bg + a.noise[(int64_t)noise_pos * a.n + e];
+    noise_pos++;
+    cgm = (a.hw.smin > cgm) ? a.hw.smin : cgm;   // max(CGM, min)
+    cgm = (a.hw.smax < cgm) ? a.hw.smax : cgm;   // min(CGM, max)
+    return cgm;
+}
+
+__device__ __forceinline__ void stats_add_row(double (&s)[NSTAT], double bg, double lbgi, double hbgi,
+                                              double ri, double reward, bool done)
+{
+    const double row = s[0];                      // index of the row being added
+    s[0] = row + 1.0;
+    s[1] += bg;
+    s[2] = (bg < s[2]) ? bg : s[2];
+    s[3] = (bg > s[3]) ? bg : s[3];
+    s[4] += lbgi; s[5] += hbgi; s[6] += ri; s[7] += reward;
+    if (bg < 50.0) s[8] += 1.0;
+    if (bg < 70.0) s[9] += 1.0;
+    if (bg >= 70.0 && bg <= 180.0) s[10] += 1.0;
+    if (bg > 180.0) s[11] += 1.0;
+    if (bg > 250.0) s[12] += 1.0;
+    if (done && s[13] < 0.0) s[13] = row;
+}
+
+__global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
+{
+    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (e >= a.n) return;
+    const ParamLoad p = param_source(a, e);
+    const double Vg = p(P_Vg);
+    double x[NX];
+    if (a.x0) {
+#pragma unroll
+        for (int i = 0; i < NX; i++) x[i] = a.x0[(int64_t)i * a.n + e];
+    } else {
+        const double *t = a.table_x0 + (int64_t)a.patient_row[e] * NX;
+#pragma unroll
+        for (int i = 0; i < NX; i++) x[i] = t[i];
+    }
+    // patient.reset(), t1dpatient.py:247-281
+    double *sd = a.sd + e;
+    int32_t *si = a.si + e;
+#pragma unroll
+    for (int i = 0; i < NX; i++) sd[(int64_t)(SD_X0 + i) * a.cap] = x[i];
+    sd[(int64_t)SD_PLANNED * a.cap] = 0.0;
+    sd[(int64_t)SD_LAST_CHO * a.cap] = 0.0;
+    sd[(int64_t)SD_LAST_QSTO * a.cap] = x[0] + x[1];
+    sd[(int64_t)SD_LAST_FOOD * a.cap] = 0.0;
+    sd[(int64_t)SD_H_CARRY * a.cap] = 0.0;
+    // env._reset() + env.reset(), env.py:119-155: two sensor samples at t = 0
+    const double bg = x[12] / Vg;
+    double lbgi, hbgi, ri;
+    risk_index(bg, lbgi, hbgi, ri);
+    int noise_pos = 0;
+    const double cgm0 = cgm_sample(a, e, bg, noise_pos);    // CGM_hist[0]
+    const double obs = cgm_sample(a, e, bg, noise_pos);     // returned observation
+    sd[(int64_t)SD_LAST_CGM * a.cap] = obs;
+    sd[(int64_t)SD_CGM_PREV * a.cap] = cgm0;
+    sd[(int64_t)SD_OBS * a.cap] = obs;
+    sd[(int64_t)SD_INFO_MEAL * a.cap] = 0.0;
+    sd[(int64_t)SD_PID_INTEG * a.cap] = 0.0;                // controller.reset(), pid_ctrller.py:38-40
+    sd[(int64_t)SD_PID_PREV * a.cap] = 0.0;
+    si[(int64_t)SI_EATING * a.cap] = 0;
+    si[(int64_t)SI_MINUTE * a.cap] = 0;
+    si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
+    si[(int64_t)SI_MEAL_POS * a.cap] = 0;
+    si[(int64_t)SI_STATUS * a.cap] = 1;
+    double s[NSTAT];
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) s[i] = 0.0;
+    s[2] = INFINITY; s[3] = -INFINITY; s[13] = -1.0;
+    stats_add_row(s, bg, lbgi, hbgi, ri, 0.0, false);
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) a.stats[(int64_t)i * a.cap + e] = s[i];
+    if (a.row0) {
+        double *r = a.row0 + e;
+        const double nan = __longlong_as_double(0x7ff8000000000000LL);
+        r[0 * a.n] = bg; r[1 * a.n] = cgm0; r[2 * a.n] = nan; r[3 * a.n] = nan;
+        r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = obs;
+        r[8 * a.n] = 0.0; r[9 * a.n] = 0.0; r[10 * a.n] = nan; r[11 * a.n] = nan;
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
+{
+    __shared__ double smem[H_COUNT * BLOCK];
+    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (e >= a.n) return;          // no block-level synchronisation below: columns are private
+    const Column<BLOCK> c{smem + threadIdx.x};
+    const ParamLoad p = param_source(a, e);
+    stage_params(c, p);
+    const double u2ss = p(P_u2ss);
+
+    double *sd = a.sd + e;
+    int32_t *si = a.si + e;
+    double x[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) x[i] = sd[(int64_t)(SD_X0 + i) * a.cap];
+    Meal meal;
+    meal.planned = sd[(int64_t)SD_PLANNED * a.cap];
+    meal.last_cho = sd[(int64_t)SD_LAST_CHO * a.cap];
+    meal.last_Qsto = sd[(int64_t)SD_LAST_QSTO * a.cap];
+    meal.last_food = sd[(int64_t)SD_LAST_FOOD * a.cap];
+    meal.eating = si[(int64_t)SI_EATING * a.cap];
+    double h_carry = sd[(int64_t)SD_H_CARRY * a.cap];
+    double last_cgm = sd[(int64_t)SD_LAST_CGM * a.cap];
+    double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
+    double obs = sd[(int64_t)SD_OBS * a.cap];
+    double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
+    double pid_integ = sd[(int64_t)SD_PID_INTEG * a.cap];
+    double pid_prev = sd[(int64_t)SD_PID_PREV * a.cap];
+    int minute = si[(int64_t)SI_MINUTE * a.cap];
+    int noise_pos = si[(int64_t)SI_NOISE_POS * a.cap];
+    int meal_pos = si[(int64_t)SI_MEAL_POS * a.cap];
+    int status = si[(int64_t)SI_STATUS * a.cap];
+    double s[NSTAT];
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) s[i] = a.stats[(int64_t)i * a.cap + e];
+
+    double ctrl[NCTRL];
+#pragma unroll
+    for (int i = 0; i < NCTRL; i++) ctrl[i] = a.ctrl_rows ? a.ctrl_rows[(int64_t)i * a.n + e] : a.ctrl[i];
+
+    const int st_i = a.hw.st;
+    const double st = (double)st_i;
+    int next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+
+    for (int k = 0; k < a.n_steps; k++) {
+        // ---- controller.policy(observation, reward, done, **info) ----
+        double a_basal, a_bolus;
+        if (a.controller == 1) {                       // BBController._bb_policy
+            a_basal = u2ss * c(H_BW) / 6000.0;
+            if (info_meal > 0.0) {
+                const double corr = (obs > 150.0 ? 1.0 : 0.0) * (obs - ctrl[0]) / ctrl[2];
+                a_bolus = (info_meal * st) / ctrl[1] + corr;
+            } else {
+                a_bolus = 0.0;
+            }
+            a_bolus = a_bolus / st;
+        } else if (a.controller == 2) {                // PIDController.policy
+            a_basal = ctrl[0] * (obs - ctrl[3]) + ctrl[1] * pid_integ + ctrl[2] * (obs - pid_prev) / st;
+            pid_prev = obs;
+            pid_integ += (obs - ctrl[3]) * st;
+            a_bolus = 0.0;
+        } else {
+            a_basal = a.act_basal[(int64_t)k * a.act_stride + e];
+            a_bolus = a.act_bolus[(int64_t)k * a.act_stride + e];
+        }
+        // ---- env.step, env.py:66-117 ----
+        const double ins = pump_quantise(a_basal, a.hw.pump[0], a.hw.pump[1], a.hw.pump[2]) +
+                           pump_quantise(a_bolus, a.hw.pump[3], a.hw.pump[4], a.hw.pump[5]);
+        double CHO = 0.0, insulin = 0.0, BG = 0.0, CGM = 0.0;
+        for (int j = 0; j < st_i; j++) {               // mini_step, env.py:48-64
+            double announced = 0.0;
+            while (next_mm >= 0 && next_mm < minute) {
+                meal_pos++;
+                next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+            }
+            if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
+            const double to_eat = meal_machine(meal, announced, x[0], x[1]);
+            const Minute m = minute_setup(c, to_eat, ins, meal.last_Qsto, meal.last_food);
+            StepCount cnt{0, 0};
+            const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt);
+            if (idid < 0 && status > 0) status = idid;
+            if (a.counters) {
+                const int64_t row = (int64_t)(k * st_i + j) * 2;
+                a.counters[row * a.n + e] = cnt.nstep;
+                a.counters[(row + 1) * a.n + e] = cnt.nrej;
+            }
+            s[14] += (double)cnt.nstep;
+            s[15] += (double)cnt.nrej;
+            minute++;
+            const double bg = x[12] / c(H_Vg);                          // t1dpatient.py:217-218
+            if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
+            CHO += announced / st; insulin += ins / st; BG += bg / st; CGM += last_cgm / st;
+        }
+        double lbgi, hbgi, ri, r_prev, r_now, t0, t1;
+        risk_index(BG, lbgi, hbgi, ri);                                  // env.py:85
+        risk_index(cgm_prev, t0, t1, r_prev);                            // risk_diff, env.py:27-33
+        risk_index(CGM, t0, t1, r_now);
+        const double reward = r_prev - r_now;
+        const bool done = (BG < 70.0) || (BG > 350.0);                   // env.py:103
+        cgm_prev = CGM; obs = CGM; info_meal = CHO;
+        stats_add_row(s, BG, lbgi, hbgi, ri, reward, done);
+        if (a.trace) {
+            double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
+            r[0 * a.n] = BG; r[1 * a.n] = CGM; r[2 * a.n] = CHO; r[3 * a.n] = insulin;
+            r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = obs;
+            r[8 * a.n] = reward; r[9 * a.n] = done ? 1.0 : 0.0; r[10 * a.n] = a_basal; r[11 * a.n] = a_bolus;
+        }
+    }
+
+#pragma unroll
+    for (int i = 0; i < NX; i++) sd[(int64_t)(SD_X0 + i) * a.cap] = x[i];
+    sd[(int64_t)SD_PLANNED * a.cap] = meal.planned;
+    sd[(int64_t)SD_LAST_CHO * a.cap] = meal.last_cho;
+    sd[(int64_t)SD_LAST_QSTO * a.cap] = meal.last_Qsto;
+    sd[(int64_t)SD_LAST_FOOD * a.cap] = meal.last_food;
+    sd[(int64_t)SD_H_CARRY * a.cap] = h_carry;
+    sd[(int64_t)SD_LAST_CGM * a.cap] = last_cgm;
+    sd[(int64_t)SD_CGM_PREV * a.cap] = cgm_prev;
+    sd[(int64_t)SD_OBS * a.cap] = obs;
+    sd[(int64_t)SD_INFO_MEAL * a.cap] = info_meal;
+    sd[(int64_t)SD_PID_INTEG * a.cap] = pid_integ;
+    sd[(int64_t)SD_PID_PREV * a.cap] = pid_prev;
+    si[(int64_t)SI_EATING * a.cap] = meal.eating;
+    si[(int64_t)SI_MINUTE * a.cap] = minute;
+    si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
+    si[(int64_t)SI_MEAL_POS * a.cap] = meal_pos;
+    si[(int64_t)SI_STATUS * a.cap] = status;
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) a.stats[(int64_t)i * a.cap + e] = s[i];
+}
+
+// ---- population statistics ------------------------------------------------------------------
+__device__ __forceinline__ double combine(int i, double u, double v)
+{
+    if (i == 2) return fmin(u, v);
+    if (i == 3) return fmax(u, v);
+    return u + v;
+}
+__device__ __forceinline__ double identity(int i)
+{
+    return i == 2 ? INFINITY : (i == 3 ? -INFINITY : 0.0);
+}
+
+constexpr int RBLOCK = 256;
+
+__global__ void __launch_bounds__(RBLOCK) reduce_partial_kernel(const ReduceArgs a)
+{
+    __shared__ double warp_part[RBLOCK / 32][NSTAT];
+    double v[NSTAT];
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) v[i] = identity(i);
+    for (int64_t e = (int64_t)blockIdx.x * RBLOCK + threadIdx.x; e < a.n; e += (int64_t)gridDim.x * RBLOCK) {
+#pragma unroll
+        for (int i = 0; i < NSTAT; i++) {
+            double u = a.stats[(int64_t)i * a.cap + e];
+            if (i == 13) u = (u >= 0.0) ? 1.0 : 0.0;      // episodes that reported done
+            v[i] = combine(i, v[i], u);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1)
+            v[i] = combine(i, v[i], __shfl_xor_sync(0xffffffffu, v[i], off));
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NSTAT; i++) warp_part[warp][i] = v[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < NSTAT) {
+        double acc = identity(threadIdx.x);
+        for (int w = 0; w < RBLOCK / 32; w++) acc = combine(threadIdx.x, acc, warp_part[w][threadIdx.x]);
+        a.partials[(int64_t)blockIdx.x * NSTAT + threadIdx.x] = acc;
+    }
+}
+
+__global__ void reduce_final_kernel(const ReduceArgs a)
+{
+    if (threadIdx.x < NSTAT) {
+        double acc = identity(threadIdx.x);
+        for (int b = 0; b < a.n_blocks; b++) acc = combine(threadIdx.x, acc, a.partials[(int64_t)b * NSTAT + threadIdx.x]);
+        a.out[threadIdx.x] = acc;
+    }
+}
+
+// ---- launchers --------------------------------------------------------------------------------
+static inline unsigned grid_for(int64_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
+
+cudaError_t launch_reset(const EpisodeArgs &a, cudaStream_t s)
+{
+    reset_kernel<<<grid_for(a.n), BLOCK, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_run(const EpisodeArgs &a, cudaStream_t s)
+{
+    run_kernel<<<grid_for(a.n), BLOCK, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+int reduce_blocks(int64_t n)
+{
+    int64_t b = (n + RBLOCK - 1) / RBLOCK;
+    if (b > 148 * 4) b = 148 * 4;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+cudaError_t launch_reduce(const ReduceArgs &a, cudaStream_t s)
+{
+    reduce_partial_kernel<<<a.n_blocks, RBLOCK, 0, s>>>(a);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    reduce_final_kernel<<<1, 32, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace SG_NS

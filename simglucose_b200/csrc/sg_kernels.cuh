@@ -1,0 +1,98 @@
+// Kernel argument blocks and launch entry points shared by sg_kernels.cu (compiled twice: with
+// -fmad=false as namespace sg_strict and with -fmad=true as namespace sg_fma) and sg_capi.cu.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace sgk {
+
+// Resident per-episode state, structure-of-arrays: sd[i * cap + e], si[i * cap + e].
+enum StateD {
+    SD_X0 = 0,                 // 13 doubles: patient state (t1dpatient.py:238-240)
+    SD_PLANNED = 13,           // planned_meal                     t1dpatient.py:225
+    SD_LAST_CHO,               // _last_action.CHO                 t1dpatient.py:106
+    SD_LAST_QSTO,              // _last_Qsto                       t1dpatient.py:90
+    SD_LAST_FOOD,              // _last_foodtaken                  t1dpatient.py:91,99
+    SD_H_CARRY,                // WORK(7) of dopri5 (only with SG_FLAG_CARRY_H)
+    SD_LAST_CGM,               // CGMSensor._last_CGM              cgm.py:33
+    SD_CGM_PREV,               // CGM_hist[-1]                     env.py:96
+    SD_OBS,                    // last observation.CGM             env.py:105,142
+    SD_INFO_MEAL,              // info['meal'] of the last step    env.py:112
+    SD_PID_INTEG,              // PIDController.integrated_state   pid_ctrller.py:15
+    SD_PID_PREV,               // PIDController.prev_state         pid_ctrller.py:16
+    SD_COUNT
+};
+enum StateI {
+    SI_EATING = 0,             // is_eating                        t1dpatient.py:92,104
+    SI_MINUTE,                 // patient.t as an integer minute   t1dpatient.py:73-75
+    SI_NOISE_POS,              // samples consumed from the noise stream
+    SI_MEAL_POS,               // next unconsumed entry of the meal table
+    SI_STATUS,                 // scipy idid of the first failed minute, else 1
+    SI_COUNT
+};
+
+constexpr int NTRACE = 12;
+constexpr int NSTAT = 16;
+constexpr int NCTRL = 4;
+constexpr int BLOCK = 128;
+
+struct Hardware {
+    int st;
+    double smin, smax;
+    double pump[6];
+};
+
+struct EpisodeArgs {
+    int64_t n;                 // episodes
+    int64_t cap;               // stride of the resident state arrays
+    double *sd;
+    int32_t *si;
+    double *stats;             // [NSTAT][cap]
+    // parameters: per-episode SoA [32][n] if non-null, else table[row * 32 + i] by patient_row
+    const double *params_soa;
+    const double *table;
+    const double *table_x0;    // [n_rows][13]
+    const int32_t *patient_row;
+    // borrowed inputs
+    const int32_t *meal_minute;
+    const double *meal_grams;
+    int32_t max_meals;
+    const double *noise;
+    int64_t n_noise;
+    Hardware hw;
+    int32_t carry_h;
+    // run
+    int32_t controller;
+    double ctrl[NCTRL];
+    const double *ctrl_rows;   // [NCTRL][n] or null
+    const double *act_basal;   // step k of episode e at act_basal[k * act_stride + e]
+    const double *act_bolus;
+    int64_t act_stride;
+    int32_t n_steps;
+    double *trace;             // [n_steps][NTRACE][n] or null
+    int32_t *counters;         // [n_steps*st][2][n] or null
+    // reset
+    const double *x0;          // [13][n] or null
+    double *row0;              // [NTRACE][n] or null
+};
+
+struct ReduceArgs {
+    int64_t n, cap;
+    const double *stats;
+    double *partials;          // [gridDim.x][NSTAT]
+    double *out;               // [NSTAT]
+    int32_t n_blocks;
+};
+
+#define SG_DECLARE_LAUNCHERS(NS)                                              \
+    namespace NS {                                                            \
+    cudaError_t launch_reset(const sgk::EpisodeArgs &a, cudaStream_t s);      \
+    cudaError_t launch_run(const sgk::EpisodeArgs &a, cudaStream_t s);        \
+    cudaError_t launch_reduce(const sgk::ReduceArgs &a, cudaStream_t s);      \
+    int reduce_blocks(int64_t n);                                             \
+    }
+
+}  // namespace sgk
+
+SG_DECLARE_LAUNCHERS(sg_strict)
+SG_DECLARE_LAUNCHERS(sg_fma)

@@ -1,0 +1,329 @@
+// Device functions of the batched UVa/Padova-2008 patient simulator (sm_100a, FP64).
+//
+// One CUDA thread owns one patient-episode: the 13-state vector and the Dormand-Prince
+// stages live in registers, the per-episode constants derived from the parameter row live in
+// a shared-memory column private to the thread (sp[i * BLOCK], conflict-free: consecutive
+// lanes hit consecutive 8-byte words).
+//
+// Reference behaviour reproduced here (paths relative to the reference root):
+//   rhs()             T1DPatient.model              simglucose/patient/t1dpatient.py:118-208
+//   dopri5_minute()   scipy ode('dopri5') as called at t1dpatient.py:276-277 (defaults) and
+//                     :110-113 (integrate one minute) -- Hairer's DOPCOR + HINIT (third party)
+//   meal_machine()    T1DPatient.step / _announce_meal          t1dpatient.py:82-107, 222-236
+//   pump_quantise()   InsulinPump.basal / .bolus        simglucose/actuator/pump.py:23-39
+//   risk_index()      risk_index([BG], 1)               simglucose/analysis/risk.py:5-17
+//
+// The operation ORDER follows the Python source (a*b/c == (a*b)/c, sums left to right) so that
+// a build with -fmad=false makes the same accept/reject decisions as the scipy path; see
+// DESIGN.md "Arithmetic contract".
+#pragma once
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+
+namespace sgk {
+
+constexpr int NX = 13;
+
+// Per-episode constants staged in shared memory (one column per thread).
+enum Hoisted {
+    H_kmax = 0, H_kmin, H_hk, H_b, H_d, H_kabs, H_fk, H_BW, H_kp1, H_kp2, H_kp3, H_Fsnc,
+    H_ke1, H_ke2, H_k1, H_k2, H_Vm0, H_Vmx, H_Km0, H_m24, H_m1, H_ka1, H_ka2, H_Vi, H_p2u,
+    H_Ib, H_ki, H_m13, H_m2, H_kad, H_kd, H_ksc, H_Vg,
+    // per-minute values (rewritten by the owning thread at every minute start)
+    H_aa, H_cc, H_bD, H_dD,
+    H_COUNT
+};
+
+// Order of the parameter row handed over the C-ABI (include/simglucose_b200.h, sg_param).
+enum Param {
+    P_BW = 0, P_u2ss, P_kmax, P_kmin, P_b, P_d, P_kabs, P_f, P_kp1, P_kp2, P_kp3, P_Fsnc,
+    P_ke1, P_ke2, P_k1, P_k2, P_Vm0, P_Vmx, P_Km0, P_m1, P_m2, P_m4, P_m30, P_ka1, P_ka2,
+    P_Vi, P_p2u, P_Ib, P_ki, P_kd, P_ksc, P_Vg,
+    P_COUNT
+};
+
+template <int BLOCK>
+struct Column {
+    double *base;   // &smem[threadIdx.x]
+    __device__ __forceinline__ double operator()(int i) const { return base[i * BLOCK]; }
+    __device__ __forceinline__ void set(int i, double v) const { base[i * BLOCK] = v; }
+};
+
+// Constants that only depend on the parameter row (t1dpatient.py:138,151,176,190,194: the
+// sub-expressions (kmax-kmin)/2, f*kabs, m2+m4, m1+m30, ka1+kd are evaluated first by Python's
+// precedence, so hoisting them is bit-safe).
+template <int BLOCK, class Load>
+__device__ __forceinline__ void stage_params(const Column<BLOCK> &c, Load p)
+{
+    const double kmax = p(P_kmax), kmin = p(P_kmin), kabs = p(P_kabs);
+    const double m1 = p(P_m1), m2 = p(P_m2), ka1 = p(P_ka1), kd = p(P_kd);
+    c.set(H_kmax, kmax); c.set(H_kmin, kmin); c.set(H_hk, (kmax - kmin) / 2.0);
+    c.set(H_b, p(P_b)); c.set(H_d, p(P_d)); c.set(H_kabs, kabs); c.set(H_fk, p(P_f) * kabs);
+    c.set(H_BW, p(P_BW)); c.set(H_kp1, p(P_kp1)); c.set(H_kp2, p(P_kp2)); c.set(H_kp3, p(P_kp3));
+    c.set(H_Fsnc, p(P_Fsnc)); c.set(H_ke1, p(P_ke1)); c.set(H_ke2, p(P_ke2));
+    c.set(H_k1, p(P_k1)); c.set(H_k2, p(P_k2)); c.set(H_Vm0, p(P_Vm0)); c.set(H_Vmx, p(P_Vmx));
+    c.set(H_Km0, p(P_Km0)); c.set(H_m24, m2 + p(P_m4)); c.set(H_m1, m1); c.set(H_ka1, ka1);
+    c.set(H_ka2, p(P_ka2)); c.set(H_Vi, p(P_Vi)); c.set(H_p2u, p(P_p2u)); c.set(H_Ib, p(P_Ib));
+    c.set(H_ki, p(P_ki)); c.set(H_m13, m1 + p(P_m30)); c.set(H_m2, m2); c.set(H_kad, ka1 + kd);
+    c.set(H_kd, kd); c.set(H_ksc, p(P_ksc)); c.set(H_Vg, p(P_Vg));
+    c.set(H_aa, 0.0); c.set(H_cc, 0.0); c.set(H_bD, 0.0); c.set(H_dD, 0.0);
+}
+
+// Inputs of the ODE that are constant over one simulated minute (t1dpatient.py:110:
+// set_f_params(action, params, last_Qsto, last_foodtaken)).
+struct Minute {
+    double d;      // action.CHO * 1000                      t1dpatient.py:121
+    double ins;    // action.insulin * 6000 / BW             t1dpatient.py:122
+    bool fed;      // Dbar > 0                               t1dpatient.py:130,135
+};
+
+template <int BLOCK>
+__device__ __forceinline__ Minute minute_setup(const Column<BLOCK> &c, double cho, double insulin,
+                                               double last_Qsto, double last_food)
+{
+    Minute m;
+    m.d = cho * 1000.0;
+    m.ins = insulin * 6000.0 / c(H_BW);
+    const double Dbar = last_Qsto + last_food * 1000.0;
+    m.fed = Dbar > 0.0;
+    if (m.fed) {                                            // t1dpatient.py:136-140
+        c.set(H_aa, 5.0 / 2.0 / (1.0 - c(H_b)) / Dbar);
+        c.set(H_cc, 5.0 / 2.0 / c(H_d) / Dbar);
+        c.set(H_bD, c(H_b) * Dbar);
+        c.set(H_dD, c(H_d) * Dbar);
+    }
+    return m;
+}
+
+__device__ __forceinline__ double mask_nonneg(double x, double dx)
+{
+    // (x >= 0) * dxdt, t1dpatient.py:167,173,179,191,195,198,202 (the sign of a zero result is
+    // not preserved; it never reaches an output)
+    return x >= 0.0 ? dx : 0.0;
+}
+
+// T1DPatient.model, t1dpatient.py:118-208.
+template <int BLOCK>
+__device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, const double (&x)[NX],
+                                    double (&dx)[NX])
+{
+    const double kmax = c(H_kmax);
+    const double qsto = x[0] + x[1];                                        // :126
+    dx[0] = -kmax * x[0] + m.d;                                             // :133
+    double kgut;
+    if (m.fed) {                                                            // :135-142
+        const double ta = tanh(c(H_aa) * (qsto - c(H_bD)));
+        const double tc = tanh(c(H_cc) * (qsto - c(H_dD)));
+        kgut = c(H_kmin) + c(H_hk) * (ta - tc + 2.0);
+    } else {
+        kgut = kmax;
+    }
+    dx[1] = kmax * x[0] - x[1] * kgut;                                      // :145
+    const double kabs = c(H_kabs);
+    dx[2] = kgut * x[1] - kabs * x[2];                                      // :148
+    const double Rat = c(H_fk) * x[2] / c(H_BW);                            // :151
+    const double EGPt = c(H_kp1) - c(H_kp2) * x[3] - c(H_kp3) * x[8];       // :153
+    const double ke2 = c(H_ke2);
+    const double Et = (x[3] > ke2) ? c(H_ke1) * (x[3] - ke2) : 0.0;         // :158-161
+    const double egp = (0.0 > EGPt) ? 0.0 : EGPt;                           // max(EGPt, 0) :165
+    const double k1 = c(H_k1), k2 = c(H_k2);
+    dx[3] = mask_nonneg(x[3], egp + Rat - c(H_Fsnc) - Et - k1 * x[3] + k2 * x[4]);   // :165-167
+    const double Vmt = c(H_Vm0) + c(H_Vmx) * x[6];                          // :169
+    const double Uidt = Vmt * x[4] / (c(H_Km0) + x[4]);                     // :171
+    dx[4] = mask_nonneg(x[4], -Uidt + k1 * x[3] - k2 * x[4]);               // :172-173
+    const double ka2 = c(H_ka2), m2 = c(H_m2);
+    dx[5] = mask_nonneg(x[5], -c(H_m24) * x[5] + c(H_m1) * x[9] + c(H_ka1) * x[10] + ka2 * x[11]);
+    const double It = x[5] / c(H_Vi);                                       // :178
+    const double p2u = c(H_p2u), ki = c(H_ki);
+    dx[6] = -p2u * x[6] + p2u * (It - c(H_Ib));                             // :182
+    dx[7] = -ki * (x[7] - It);                                              // :185
+    dx[8] = -ki * (x[8] - x[7]);                                            // :187
+    dx[9] = mask_nonneg(x[9], -c(H_m13) * x[9] + m2 * x[5]);                // :190-191
+    const double kd = c(H_kd);
+    dx[10] = mask_nonneg(x[10], m.ins - c(H_kad) * x[10]);                  // :194-195
+    dx[11] = mask_nonneg(x[11], kd * x[10] - ka2 * x[11]);                  // :197-198
+    const double ksc = c(H_ksc);
+    dx[12] = mask_nonneg(x[12], -ksc * x[12] + ksc * x[3]);                 // :201-202
+}
+
+// InsulinPump.basal / .bolus, pump.py:23-39.  np.round == round-half-even == rint().
+__device__ __forceinline__ double pump_quantise(double amount, double vmin, double vmax, double inc)
+{
+    double v = amount * 6000.0;
+    v = rint(v / inc) * inc;
+    v = v / 6000.0;
+    v = (vmax < v) ? vmax : v;     // Python min(v, vmax)
+    v = (vmin > v) ? vmin : v;     // Python max(v, vmin)
+    return v;
+}
+
+// risk_index([BG], 1), risk.py:5-17 (NaN -> 0 via nan_to_num; BG < 1 gives log < 0 -> pow NaN).
+__device__ __forceinline__ void risk_index(double bg, double &lbgi, double &hbgi, double &ri)
+{
+    const double f = 1.509 * (pow(log(bg), 1.084) - 5.381);
+    lbgi = (f < 0.0) ? 10.0 * (f * f) : 0.0;
+    hbgi = (f > 0.0) ? 10.0 * (f * f) : 0.0;
+    if (isinf(lbgi)) lbgi = DBL_MAX;
+    if (isinf(hbgi)) hbgi = DBL_MAX;
+    ri = lbgi + hbgi;
+}
+
+// Meal state machine of T1DPatient.step (t1dpatient.py:82-107) with _announce_meal (:222-236).
+struct Meal {
+    double planned, last_cho, last_Qsto, last_food;
+    int eating;
+};
+
+__device__ __forceinline__ double meal_machine(Meal &s, double announced, double x0, double x1)
+{
+    double to_eat;
+    s.planned += announced;
+    if (s.planned > 0.0) {
+        to_eat = (s.planned < 5.0) ? s.planned : 5.0;       // min(EAT_RATE, planned)
+        s.planned -= to_eat;
+        s.planned = (0.0 > s.planned) ? 0.0 : s.planned;
+    } else {
+        to_eat = 0.0;
+    }
+    if (to_eat > 0.0 && s.last_cho <= 0.0) {                // onset :88-92
+        s.last_Qsto = x0 + x1;
+        s.last_food = 0.0;
+        s.eating = 1;
+    }
+    if (s.eating) s.last_food += to_eat;                    // :98-99
+    if (to_eat <= 0.0 && s.last_cho > 0.0) s.eating = 0;    // :102-104
+    s.last_cho = to_eat;
+    return to_eat;
+}
+
+// ---- DOPRI5 (Hairer, Norsett & Wanner; scipy _dop.dopri5), scipy defaults ----------------
+constexpr double A21 = 0.2, A31 = 3.0 / 40.0, A32 = 9.0 / 40.0, A41 = 44.0 / 45.0,
+    A42 = -56.0 / 15.0, A43 = 32.0 / 9.0, A51 = 19372.0 / 6561.0, A52 = -25360.0 / 2187.0,
+    A53 = 64448.0 / 6561.0, A54 = -212.0 / 729.0, A61 = 9017.0 / 3168.0, A62 = -355.0 / 33.0,
+    A63 = 46732.0 / 5247.0, A64 = 49.0 / 176.0, A65 = -5103.0 / 18656.0, A71 = 35.0 / 384.0,
+    A73 = 500.0 / 1113.0, A74 = 125.0 / 192.0, A75 = -2187.0 / 6784.0, A76 = 11.0 / 84.0,
+    E1 = 71.0 / 57600.0, E3 = -71.0 / 16695.0, E4 = 71.0 / 1920.0, E5 = -17253.0 / 339200.0,
+    E6 = 22.0 / 525.0, E7 = -1.0 / 40.0;
+constexpr double RTOL = 1e-6, ATOL = 1e-12, UROUND = 2.3e-16;
+constexpr int NMAX = 500;
+
+struct StepCount { int nstep, nrej; };
+
+// HINIT: initial step size guess.  f0 = f(x, y).
+template <int BLOCK>
+__device__ __forceinline__ double hinit(const Column<BLOCK> &c, const Minute &m,
+                                        const double (&y)[NX], const double (&f0)[NX], double hmax)
+{
+    double dnf = 0.0, dny = 0.0;
+#pragma unroll
+    for (int i = 0; i < NX; i++) {
+        const double sk = ATOL + RTOL * fabs(y[i]);
+        const double a = f0[i] / sk, b = y[i] / sk;
+        dnf = dnf + a * a;
+        dny = dny + b * b;
+    }
+    double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+    h = fmin(h, hmax);
+    double y1[NX], f1[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) y1[i] = y[i] + h * f0[i];
+    rhs(c, m, y1, f1);
+    double der2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < NX; i++) {
+        const double sk = ATOL + RTOL * fabs(y[i]);
+        const double a = (f1[i] - f0[i]) / sk;
+        der2 = der2 + a * a;
+    }
+    der2 = sqrt(der2) / h;
+    const double der12 = fmax(fabs(der2), sqrt(dnf));
+    const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : pow(0.01 / der12, 1.0 / 5.0);
+    return fmin(fmin(100.0 * fabs(h), h1), hmax);
+}
+
+// One call of ode('dopri5').integrate(t + 1).  Returns idid (1 ok, -2 nmax, -3 step too small).
+// h_carry: WORK(7) of the Fortran (kept across calls by scipy 1.6.3, zero in scipy >= 1.7).
+template <int BLOCK>
+__device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minute &m, double (&y)[NX],
+                                             double t0, bool carry_h, double &h_carry, StepCount &cnt)
+{
+    const double beta = 0.04, safe = 0.9;
+    const double expo1 = 0.2 - beta * 0.75;
+    const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
+    double x = t0;
+    const double xend = t0 + 1.0;
+    const double hmax = fabs(xend - x);
+    double facold = 1.0e-4;
+    bool last = false, reject = false;
+    int nstep = 0, naccpt = 0, idid;
+    double k1[NX], k2[NX], k3[NX], k4[NX], k5[NX], k6[NX], y1[NX];
+
+    rhs(c, m, y, k1);
+    double h = carry_h ? h_carry : 0.0;
+    if (h == 0.0) h = hinit(c, m, y, k1, hmax);
+
+    for (;;) {
+        if (nstep > NMAX) { idid = -2; break; }
+        if (0.1 * fabs(h) <= fabs(x) * UROUND) { idid = -3; break; }
+        if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
+        nstep++;
+#pragma unroll
+        for (int i = 0; i < NX; i++) y1[i] = y[i] + h * A21 * k1[i];
+        rhs(c, m, y1, k2);
+#pragma unroll
+        for (int i = 0; i < NX; i++) y1[i] = y[i] + h * (A31 * k1[i] + A32 * k2[i]);
+        rhs(c, m, y1, k3);
+#pragma unroll
+        for (int i = 0; i < NX; i++) y1[i] = y[i] + h * (A41 * k1[i] + A42 * k2[i] + A43 * k3[i]);
+        rhs(c, m, y1, k4);
+#pragma unroll
+        for (int i = 0; i < NX; i++)
+            y1[i] = y[i] + h * (A51 * k1[i] + A52 * k2[i] + A53 * k3[i] + A54 * k4[i]);
+        rhs(c, m, y1, k5);
+#pragma unroll
+        for (int i = 0; i < NX; i++)   // ysti shares storage with y1
+            y1[i] = y[i] + h * (A61 * k1[i] + A62 * k2[i] + A63 * k3[i] + A64 * k4[i] + A65 * k5[i]);
+        const double xph = x + h;
+        rhs(c, m, y1, k6);
+#pragma unroll
+        for (int i = 0; i < NX; i++)
+            y1[i] = y[i] + h * (A71 * k1[i] + A73 * k3[i] + A74 * k4[i] + A75 * k5[i] + A76 * k6[i]);
+        rhs(c, m, y1, k2);                                   // FSAL
+        double err = 0.0;
+#pragma unroll
+        for (int i = 0; i < NX; i++) {
+            const double e = (E1 * k1[i] + E3 * k3[i] + E4 * k4[i] + E5 * k5[i] + E6 * k6[i] + E7 * k2[i]) * h;
+            const double sk = ATOL + RTOL * fmax(fabs(y[i]), fabs(y1[i]));
+            const double a = e / sk;
+            err = err + a * a;
+        }
+        err = sqrt(err / (double)NX);
+        const double fac11 = pow(err, expo1);
+        double fac = fac11 / pow(facold, beta);
+        fac = fmax(facc2, fmin(facc1, fac / safe));
+        double hnew = h / fac;
+        if (err <= 1.0) {
+            facold = fmax(err, 1.0e-4);
+            naccpt++;
+#pragma unroll
+            for (int i = 0; i < NX; i++) { k1[i] = k2[i]; y[i] = y1[i]; }
+            x = xph;
+            if (last) { h = hnew; idid = 1; break; }
+            if (fabs(hnew) > hmax) hnew = hmax;
+            if (reject) hnew = fmin(fabs(hnew), fabs(h));
+            reject = false;
+        } else {
+            hnew = h / fmin(facc1, fac11 / safe);
+            reject = true;
+            if (naccpt >= 1) cnt.nrej++;
+            last = false;
+        }
+        h = hnew;
+    }
+    if (carry_h) h_carry = h;
+    cnt.nstep += nstep;
+    return idid;
+}
+
+}  // namespace sgk

@@ -1,0 +1,184 @@
+"""BatchEngine -- host-side owner of one C-ABI handle (one GPU, one population of episodes).
+
+PyTorch is used for device memory, streams and host<->device copies only; every simulated minute is
+computed by the CUDA library behind include/simglucose_b200.h.  All arrays that cross into the
+library are structure-of-arrays device tensors of shape [rows, n_episodes].
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _capi
+from . import params as P
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class BatchEngine:
+    """n_episodes independent closed loops resident on one GPU.
+
+    Mirrors, for a whole population at once, what the reference does per patient with
+    T1DSimEnv (simulation/env.py:36-180) driven by SimObj.simulate (simulation/sim_engine.py:29-39).
+    """
+
+    def __init__(self, capacity, device=0, carry_h=False, fma=False, sensor='Dexcom', pump='Insulet'):
+        if not torch.cuda.is_available():
+            raise _capi.SgError('simglucose_b200 needs a CUDA device (there is no CPU fallback)')
+        self.lib = _capi.load()
+        self.device = torch.device('cuda', device)
+        self.capacity = int(capacity)
+        self.flags = (_capi.FLAG_CARRY_H if carry_h else 0) | (_capi.FLAG_FMA if fma else 0)
+        h = C.c_void_p()
+        _capi.check(self.lib.sg_create(self.device.index, self.capacity, self.flags, C.byref(h)))
+        self._h = h
+        self.n = 0
+        self._keep = {}
+        self.set_hardware(sensor, pump)
+        tbl, x0 = P.cohort_table()
+        self.load_table(tbl, x0)
+
+    # -- configuration ---------------------------------------------------------------------------
+    def set_hardware(self, sensor='Dexcom', pump='Insulet'):
+        s = P.sensor_params(sensor) if isinstance(sensor, str) else sensor
+        p = P.pump_params(pump) if isinstance(pump, str) else pump
+        hw = _capi.Hardware()
+        hw.sample_time = int(s['sample_time'])
+        hw.sensor_min, hw.sensor_max = float(s['min']), float(s['max'])
+        hw.pump[:] = [p['min_basal'], p['max_basal'], p['inc_basal'], p['min_bolus'], p['max_bolus'], p['inc_bolus']]
+        _capi.check(self.lib.sg_set_hardware(self._h, C.byref(hw)))
+        self.sample_time = hw.sample_time
+        self.sensor, self.pump = s, p
+
+    def load_table(self, table, x0):
+        table = np.ascontiguousarray(table, dtype=np.float64)
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        assert table.ndim == 2 and table.shape[1] == _capi.NPARAM and x0.shape == (table.shape[0], _capi.NX)
+        dp = C.POINTER(C.c_double)
+        _capi.check(self.lib.sg_load_params(self._h, table.ctypes.data_as(dp), x0.ctypes.data_as(dp), table.shape[0]))
+        self.n_rows = table.shape[0]
+
+    # -- helpers -----------------------------------------------------------------------------------
+    def _dev(self, a, dtype, rows=None):
+        """-> contiguous device tensor [rows, n]; accepts numpy / torch, host / device."""
+        if a is None:
+            return None
+        t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+        t = t.to(device=self.device, dtype=dtype, non_blocking=True)
+        if t.ndim == 1:
+            t = t.unsqueeze(0)
+        t = t.contiguous()
+        assert t.shape[-1] == self.n, 'last dimension must be n_episodes (structure-of-arrays)'
+        if rows is not None:
+            assert t.shape[0] == rows, (t.shape, rows)
+        return t
+
+    def empty(self, *rows, dtype=torch.float64):
+        return torch.empty(*rows, self.n, dtype=dtype, device=self.device)
+
+    # -- episode life cycle --------------------------------------------------------------------
+    def reset(self, patient_row, noise, meal_minute=None, meal_grams=None, x0=None, params=None, row0=True):
+        """T1DSimEnv.reset for the whole population.  All arrays SoA: [rows, E].
+
+        patient_row [E] int32; noise [n_noise, E]; meal_minute/meal_grams [M, E]; x0 [13, E] (None: table);
+        params [32, E] (None: table).  Returns history row 0 as a [NTRACE, E] tensor (or None)."""
+        pr = patient_row if isinstance(patient_row, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(patient_row))
+        self.n = int(pr.numel())
+        if self.n < 1 or self.n > self.capacity:
+            raise ValueError('n_episodes %d outside 1..capacity %d' % (self.n, self.capacity))
+        pr = pr.to(device=self.device, dtype=torch.int32).reshape(self.n).contiguous()
+        nz = self._dev(noise, torch.float64)
+        mm = self._dev(meal_minute, torch.int32)
+        mg = self._dev(meal_grams, torch.float64)
+        max_meals = 0 if mm is None else mm.shape[0]
+        if mm is not None:
+            assert mg is not None and mg.shape == mm.shape
+        x0t = self._dev(x0, torch.float64, _capi.NX)
+        pt = self._dev(params, torch.float64, _capi.NPARAM)
+        r0 = self.empty(_capi.NTRACE) if row0 else None
+        # the library borrows these until the next reset
+        self._keep = dict(pr=pr, nz=nz, mm=mm, mg=mg, x0=x0t, pt=pt)
+        _capi.check(self.lib.sg_reset(self._h, self.n, _ptr(pr), _ptr(pt), _ptr(x0t), _ptr(mm), _ptr(mg), max_meals,
+                                      _ptr(nz), nz.shape[0], _ptr(r0), _stream_ptr()))
+        self.steps_done = 0
+        return r0
+
+    def step(self, basal, bolus, out=None):
+        """T1DSimEnv.step for every episode: one env-step with Action(basal[e], bolus[e])."""
+        b = self._dev(basal, torch.float64, 1)
+        o = self._dev(bolus, torch.float64, 1)
+        if out is None:
+            out = self.empty(_capi.NTRACE)
+        _capi.check(self.lib.sg_step(self._h, _ptr(b), _ptr(o), _ptr(out), _stream_ptr()))
+        self.steps_done += 1
+        return out
+
+    def run(self, n_steps, controller='bb', ctrl=None, ctrl_rows=None, actions=None, trace=True, counters=False):
+        """SimObj.simulate for every episode, n_steps env-steps in one launch.
+
+        controller: 'bb' (ctrl = target, CR, CF), 'pid' (ctrl = P, I, D, target) or 'actions'
+        (actions [n_steps, 2, E]).  ctrl_rows [4, E] overrides ctrl per episode.
+        Returns dict(trace [n_steps, NTRACE, E] | None, counters [n_steps*st, 2, E] | None)."""
+        kind = {'actions': _capi.CTRL_ACTIONS, 'bb': _capi.CTRL_BB, 'pid': _capi.CTRL_PID}[controller]
+        cbuf = None
+        if ctrl is not None:
+            c = list(ctrl) + [0.0] * (_capi.NCTRL - len(ctrl))
+            cbuf = (C.c_double * _capi.NCTRL)(*c)
+        cr = self._dev(ctrl_rows, torch.float64, _capi.NCTRL)
+        act = None
+        if actions is not None:
+            act = actions if isinstance(actions, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(actions))
+            act = act.to(device=self.device, dtype=torch.float64).contiguous()
+            assert tuple(act.shape) == (n_steps, 2, self.n)
+        tr = torch.empty(n_steps, _capi.NTRACE, self.n, dtype=torch.float64, device=self.device) if trace else None
+        cn = (torch.empty(n_steps * self.sample_time, 2, self.n, dtype=torch.int32, device=self.device)
+              if counters else None)
+        _capi.check(self.lib.sg_run(self._h, kind, cbuf, _ptr(cr), _ptr(act), int(n_steps), _ptr(tr), _ptr(cn),
+                                    _stream_ptr()))
+        self.steps_done += n_steps
+        return dict(trace=tr, counters=cn)
+
+    # -- readers -----------------------------------------------------------------------------------
+    def state(self):
+        out = self.empty(_capi.NX)
+        _capi.check(self.lib.sg_get_state(self._h, _ptr(out), _stream_ptr()))
+        return out
+
+    def stats(self):
+        out = self.empty(_capi.NSTAT)
+        _capi.check(self.lib.sg_get_stats(self._h, _ptr(out), _stream_ptr()))
+        return out
+
+    def status(self):
+        out = torch.empty(self.n, dtype=torch.int32, device=self.device)
+        _capi.check(self.lib.sg_get_status(self._h, _ptr(out), _stream_ptr()))
+        return out
+
+    def reduce_stats(self, out=None):
+        """Population aggregate [NSTAT] (device tensor): sums, BG extrema, #episodes done."""
+        if out is None:
+            out = torch.empty(_capi.NSTAT, dtype=torch.float64, device=self.device)
+        _capi.check(self.lib.sg_reduce_stats(self._h, _ptr(out), _stream_ptr()))
+        return out
+
+    @property
+    def launches(self):
+        return int(self.lib.sg_launch_count(self._h))
+
+    def close(self):
+        if getattr(self, '_h', None) is not None and self._h:
+            self.lib.sg_destroy(self._h)
+            self._h = None
+        self._keep = {}
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
