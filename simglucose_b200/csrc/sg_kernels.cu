@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
 
 __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
 {
-    __shared__ double smem[H_COUNT * BLOCK];
+    extern __shared__ double smem[];   // H_COUNT rows x BLOCK columns
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     if (e >= a.n) return;          // no block-level synchronisation below: columns are private
     const Column<BLOCK> c{smem + threadIdx.x};
@@ -313,7 +313,14 @@ cudaError_t launch_reset(const EpisodeArgs &a, cudaStream_t s)
 
 cudaError_t launch_run(const EpisodeArgs &a, cudaStream_t s)
 {
-    run_kernel<<<grid_for(a.n), BLOCK, 0, s>>>(a);
+    constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    run_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
     return cudaGetLastError();
 }
 

@@ -32,7 +32,10 @@ enum Hoisted {
     H_Ib, H_ki, H_m13, H_m2, H_kad, H_kd, H_ksc, H_Vg,
     // per-minute values (rewritten by the owning thread at every minute start)
     H_aa, H_cc, H_bD, H_dD,
-    H_COUNT
+    // scratch rows: the 13-component error / HINIT norms run as rolled loops over this staging area so
+    // that each IEEE division is emitted once instead of 13 times (instruction-cache footprint)
+    H_SCRATCH,
+    H_COUNT = H_SCRATCH + 2 * NX
 };
 
 // Order of the parameter row handed over the C-ABI (include/simglucose_b200.h, sg_param).
@@ -198,52 +201,60 @@ __device__ __forceinline__ double meal_machine(Meal &s, double announced, double
 }
 
 // ---- DOPRI5 (Hairer, Norsett & Wanner; scipy _dop.dopri5), scipy defaults ----------------
-constexpr double A21 = 0.2, A31 = 3.0 / 40.0, A32 = 9.0 / 40.0, A41 = 44.0 / 45.0,
-    A42 = -56.0 / 15.0, A43 = 32.0 / 9.0, A51 = 19372.0 / 6561.0, A52 = -25360.0 / 2187.0,
-    A53 = 64448.0 / 6561.0, A54 = -212.0 / 729.0, A61 = 9017.0 / 3168.0, A62 = -355.0 / 33.0,
-    A63 = 46732.0 / 5247.0, A64 = 49.0 / 176.0, A65 = -5103.0 / 18656.0, A71 = 35.0 / 384.0,
-    A73 = 500.0 / 1113.0, A74 = 125.0 / 192.0, A75 = -2187.0 / 6784.0, A76 = 11.0 / 84.0,
-    E1 = 71.0 / 57600.0, E3 = -71.0 / 16695.0, E4 = 71.0 / 1920.0, E5 = -17253.0 / 339200.0,
-    E6 = 22.0 / 525.0, E7 = -1.0 / 40.0;
-constexpr double RTOL = 1e-6, ATOL = 1e-12, UROUND = 2.3e-16;
+// The coefficients live in constant memory so that DMUL/DFMA/DADD read them as c[bank][offset] operands;
+// as 64-bit immediates each use costs two extra UMOV instructions (14 % of the instructions executed by
+// the first version of this kernel, profiles/r01_*).
+enum Coef {
+    K_A21, K_A31, K_A32, K_A41, K_A42, K_A43, K_A51, K_A52, K_A53, K_A54, K_A61, K_A62, K_A63, K_A64, K_A65,
+    K_A71, K_A73, K_A74, K_A75, K_A76, K_E1, K_E3, K_E4, K_E5, K_E6, K_E7, K_RTOL, K_ATOL, K_COUNT
+};
+static __constant__ double KC[K_COUNT] = {
+    0.2, 3.0 / 40.0, 9.0 / 40.0, 44.0 / 45.0, -56.0 / 15.0, 32.0 / 9.0, 19372.0 / 6561.0, -25360.0 / 2187.0,
+    64448.0 / 6561.0, -212.0 / 729.0, 9017.0 / 3168.0, -355.0 / 33.0, 46732.0 / 5247.0, 49.0 / 176.0,
+    -5103.0 / 18656.0, 35.0 / 384.0, 500.0 / 1113.0, 125.0 / 192.0, -2187.0 / 6784.0, 11.0 / 84.0,
+    71.0 / 57600.0, -71.0 / 16695.0, 71.0 / 1920.0, -17253.0 / 339200.0, 22.0 / 525.0, -1.0 / 40.0,
+    1e-6, 1e-12};
+#define A21 KC[K_A21]
+#define A31 KC[K_A31]
+#define A32 KC[K_A32]
+#define A41 KC[K_A41]
+#define A42 KC[K_A42]
+#define A43 KC[K_A43]
+#define A51 KC[K_A51]
+#define A52 KC[K_A52]
+#define A53 KC[K_A53]
+#define A54 KC[K_A54]
+#define A61 KC[K_A61]
+#define A62 KC[K_A62]
+#define A63 KC[K_A63]
+#define A64 KC[K_A64]
+#define A65 KC[K_A65]
+#define A71 KC[K_A71]
+#define A73 KC[K_A73]
+#define A74 KC[K_A74]
+#define A75 KC[K_A75]
+#define A76 KC[K_A76]
+#define E1 KC[K_E1]
+#define E3 KC[K_E3]
+#define E4 KC[K_E4]
+#define E5 KC[K_E5]
+#define E6 KC[K_E6]
+#define E7 KC[K_E7]
+#define RTOL KC[K_RTOL]
+#define ATOL KC[K_ATOL]
+constexpr double UROUND = 2.3e-16;
 constexpr int NMAX = 500;
 
 struct StepCount { int nstep, nrej; };
 
-// HINIT: initial step size guess.  f0 = f(x, y).
-template <int BLOCK>
-__device__ __forceinline__ double hinit(const Column<BLOCK> &c, const Minute &m,
-                                        const double (&y)[NX], const double (&f0)[NX], double hmax)
-{
-    double dnf = 0.0, dny = 0.0;
-#pragma unroll
-    for (int i = 0; i < NX; i++) {
-        const double sk = ATOL + RTOL * fabs(y[i]);
-        const double a = f0[i] / sk, b = y[i] / sk;
-        dnf = dnf + a * a;
-        dny = dny + b * b;
-    }
-    double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
-    h = fmin(h, hmax);
-    double y1[NX], f1[NX];
-#pragma unroll
-    for (int i = 0; i < NX; i++) y1[i] = y[i] + h * f0[i];
-    rhs(c, m, y1, f1);
-    double der2 = 0.0;
-#pragma unroll
-    for (int i = 0; i < NX; i++) {
-        const double sk = ATOL + RTOL * fabs(y[i]);
-        const double a = (f1[i] - f0[i]) / sk;
-        der2 = der2 + a * a;
-    }
-    der2 = sqrt(der2) / h;
-    const double der12 = fmax(fabs(der2), sqrt(dnf));
-    const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : pow(0.01 / der12, 1.0 / 5.0);
-    return fmin(fmin(100.0 * fabs(h), h1), hmax);
-}
-
-// One call of ode('dopri5').integrate(t + 1).  Returns idid (1 ok, -2 nmax, -3 step too small).
+// One call of ode('dopri5').integrate(t + 1): k1 = f(y), HINIT (initial step size guess) unless a step
+// size is carried over, then the adaptive step loop.  Returns idid (1 ok, -2 nmax, -3 step too small).
 // h_carry: WORK(7) of the Fortran (kept across calls by scipy 1.6.3, zero in scipy >= 1.7).
+//
+// Written as a phase machine around ONE instance of the RHS: phase 0 evaluates k1, phase 1 the HINIT
+// probe f(y + h*k1), phases 2..7 the stages k2..k7.  Eight inlined copies of the RHS (two tanh each)
+// made a 140 KB kernel that stalled on instruction fetch (profiles/r01_*); this form is ~4x smaller.
+// All lanes of a warp walk the phases together, so the switches are uniform branches.
 template <int BLOCK>
 __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minute &m, double (&y)[NX],
                                              double t0, bool carry_h, double &h_carry, StepCount &cnt)
@@ -256,70 +267,169 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     const double hmax = fabs(xend - x);
     double facold = 1.0e-4;
     bool last = false, reject = false;
-    int nstep = 0, naccpt = 0, idid;
-    double k1[NX], k2[NX], k3[NX], k4[NX], k5[NX], k6[NX], y1[NX];
+    int nstep = 0, naccpt = 0, idid = 0, phase = 0;
+    double k1[NX], k2[NX], k3[NX], k4[NX], k5[NX], k6[NX], yt[NX], kt[NX];
+    double h = 0.0, dnf = 0.0;
 
-    rhs(c, m, y, k1);
-    double h = carry_h ? h_carry : 0.0;
-    if (h == 0.0) h = hinit(c, m, y, k1, hmax);
+#pragma unroll 1
+    while (idid == 0) {
+        switch (phase) {
+        case 0:
+#pragma unroll
+            for (int i = 0; i < NX; i++) yt[i] = y[i];
+            break;
+        case 1:
+#pragma unroll
+            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * k1[i];
+            break;
+        case 2:
+#pragma unroll
+            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * A21 * k1[i];
+            break;
+        case 3:
+#pragma unroll
+            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A31 * k1[i] + A32 * k2[i]);
+            break;
+        case 4:
+#pragma unroll
+            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A41 * k1[i] + A42 * k2[i] + A43 * k3[i]);
+            break;
+        case 5:
+#pragma unroll
+            for (int i = 0; i < NX; i++)
+                yt[i] = y[i] + h * (A51 * k1[i] + A52 * k2[i] + A53 * k3[i] + A54 * k4[i]);
+            break;
+        case 6:
+#pragma unroll
+            for (int i = 0; i < NX; i++)
+                yt[i] = y[i] + h * (A61 * k1[i] + A62 * k2[i] + A63 * k3[i] + A64 * k4[i] + A65 * k5[i]);
+            break;
+        default:
+#pragma unroll
+            for (int i = 0; i < NX; i++)
+                yt[i] = y[i] + h * (A71 * k1[i] + A73 * k3[i] + A74 * k4[i] + A75 * k5[i] + A76 * k6[i]);
+            break;
+        }
 
-    for (;;) {
-        if (nstep > NMAX) { idid = -2; break; }
-        if (0.1 * fabs(h) <= fabs(x) * UROUND) { idid = -3; break; }
-        if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
-        nstep++;
+        rhs(c, m, yt, kt);
+
+        bool begin_step = false;
+        switch (phase) {
+        case 0: {
 #pragma unroll
-        for (int i = 0; i < NX; i++) y1[i] = y[i] + h * A21 * k1[i];
-        rhs(c, m, y1, k2);
+            for (int i = 0; i < NX; i++) k1[i] = kt[i];
+            h = carry_h ? h_carry : 0.0;
+            if (h == 0.0) {                                  // HINIT, first half
+                double dny = 0.0;
+                dnf = 0.0;
 #pragma unroll
-        for (int i = 0; i < NX; i++) y1[i] = y[i] + h * (A31 * k1[i] + A32 * k2[i]);
-        rhs(c, m, y1, k3);
+                for (int i = 0; i < NX; i++) { c.set(H_SCRATCH + i, y[i]); c.set(H_SCRATCH + NX + i, k1[i]); }
+#pragma unroll 1
+                for (int i = 0; i < NX; i++) {
+                    const double yi = c(H_SCRATCH + i);
+                    const double sk = ATOL + RTOL * fabs(yi);
+                    const double a = c(H_SCRATCH + NX + i) / sk, b = yi / sk;
+                    dnf = dnf + a * a;
+                    dny = dny + b * b;
+                }
+                h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+                h = fmin(h, hmax);
+                phase = 1;
+            } else {
+                begin_step = true;
+            }
+        } break;
+        case 1: {                                            // HINIT, second half: kt = f(x + h, y + h*k1)
+            double der2 = 0.0;
 #pragma unroll
-        for (int i = 0; i < NX; i++) y1[i] = y[i] + h * (A41 * k1[i] + A42 * k2[i] + A43 * k3[i]);
-        rhs(c, m, y1, k4);
+            for (int i = 0; i < NX; i++) { c.set(H_SCRATCH + i, y[i]); c.set(H_SCRATCH + NX + i, kt[i] - k1[i]); }
+#pragma unroll 1
+            for (int i = 0; i < NX; i++) {
+                const double sk = ATOL + RTOL * fabs(c(H_SCRATCH + i));
+                const double a = c(H_SCRATCH + NX + i) / sk;
+                der2 = der2 + a * a;
+            }
+            der2 = sqrt(der2) / h;
+            const double der12 = fmax(fabs(der2), sqrt(dnf));
+            const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : pow(0.01 / der12, 1.0 / 5.0);
+            h = fmin(fmin(100.0 * fabs(h), h1), hmax);
+            begin_step = true;
+        } break;
+        case 2:
 #pragma unroll
-        for (int i = 0; i < NX; i++)
-            y1[i] = y[i] + h * (A51 * k1[i] + A52 * k2[i] + A53 * k3[i] + A54 * k4[i]);
-        rhs(c, m, y1, k5);
+            for (int i = 0; i < NX; i++) k2[i] = kt[i];
+            phase = 3;
+            break;
+        case 3:
 #pragma unroll
-        for (int i = 0; i < NX; i++)   // ysti shares storage with y1
-            y1[i] = y[i] + h * (A61 * k1[i] + A62 * k2[i] + A63 * k3[i] + A64 * k4[i] + A65 * k5[i]);
-        const double xph = x + h;
-        rhs(c, m, y1, k6);
+            for (int i = 0; i < NX; i++) k3[i] = kt[i];
+            phase = 4;
+            break;
+        case 4:
 #pragma unroll
-        for (int i = 0; i < NX; i++)
-            y1[i] = y[i] + h * (A71 * k1[i] + A73 * k3[i] + A74 * k4[i] + A75 * k5[i] + A76 * k6[i]);
-        rhs(c, m, y1, k2);                                   // FSAL
-        double err = 0.0;
+            for (int i = 0; i < NX; i++) k4[i] = kt[i];
+            phase = 5;
+            break;
+        case 5:
 #pragma unroll
-        for (int i = 0; i < NX; i++) {
-            const double e = (E1 * k1[i] + E3 * k3[i] + E4 * k4[i] + E5 * k5[i] + E6 * k6[i] + E7 * k2[i]) * h;
-            const double sk = ATOL + RTOL * fmax(fabs(y[i]), fabs(y1[i]));
-            const double a = e / sk;
-            err = err + a * a;
+            for (int i = 0; i < NX; i++) k5[i] = kt[i];
+            phase = 6;
+            break;
+        case 6:
+#pragma unroll
+            for (int i = 0; i < NX; i++) k6[i] = kt[i];
+            phase = 7;
+            break;
+        default: {                                           // kt = k7 = f(x + h, y1): error estimate + control
+            double err = 0.0;
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                c.set(H_SCRATCH + i, (E1 * k1[i] + E3 * k3[i] + E4 * k4[i] + E5 * k5[i] + E6 * k6[i] + E7 * kt[i]) * h);
+                c.set(H_SCRATCH + NX + i, ATOL + RTOL * fmax(fabs(y[i]), fabs(yt[i])));
+            }
+#pragma unroll 1
+            for (int i = 0; i < NX; i++) {
+                const double a = c(H_SCRATCH + i) / c(H_SCRATCH + NX + i);
+                err = err + a * a;
+            }
+            err = sqrt(err / (double)NX);
+            const double fac11 = pow(err, expo1);
+            double fac = fac11 / pow(facold, beta);
+            fac = fmax(facc2, fmin(facc1, fac / safe));
+            double hnew = h / fac;
+            if (err <= 1.0) {
+                facold = fmax(err, 1.0e-4);
+                naccpt++;
+#pragma unroll
+                for (int i = 0; i < NX; i++) { k1[i] = kt[i]; y[i] = yt[i]; }   // FSAL
+                x = x + h;
+                if (last) {
+                    idid = 1;
+                } else {
+                    if (fabs(hnew) > hmax) hnew = hmax;
+                    if (reject) hnew = fmin(fabs(hnew), fabs(h));
+                    reject = false;
+                    begin_step = true;
+                }
+            } else {
+                hnew = h / fmin(facc1, fac11 / safe);
+                reject = true;
+                if (naccpt >= 1) cnt.nrej++;
+                last = false;
+                begin_step = true;
+            }
+            h = hnew;
+        } break;
         }
-        err = sqrt(err / (double)NX);
-        const double fac11 = pow(err, expo1);
-        double fac = fac11 / pow(facold, beta);
-        fac = fmax(facc2, fmin(facc1, fac / safe));
-        double hnew = h / fac;
-        if (err <= 1.0) {
-            facold = fmax(err, 1.0e-4);
-            naccpt++;
-#pragma unroll
-            for (int i = 0; i < NX; i++) { k1[i] = k2[i]; y[i] = y1[i]; }
-            x = xph;
-            if (last) { h = hnew; idid = 1; break; }
-            if (fabs(hnew) > hmax) hnew = hmax;
-            if (reject) hnew = fmin(fabs(hnew), fabs(h));
-            reject = false;
-        } else {
-            hnew = h / fmin(facc1, fac11 / safe);
-            reject = true;
-            if (naccpt >= 1) cnt.nrej++;
-            last = false;
+        if (begin_step) {
+            if (nstep > NMAX) idid = -2;
+            else if (0.1 * fabs(h) <= fabs(x) * UROUND) idid = -3;
+            else {
+                if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
+                nstep++;
+                phase = 2;
+            }
         }
-        h = hnew;
     }
     if (carry_h) h_carry = h;
     cnt.nstep += nstep;
