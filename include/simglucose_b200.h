@@ -117,6 +117,40 @@ int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const 
  * sample_time minutes with Action(basal[e], bolus[e]).  out [SG_NTRACE][E] = the new history row. */
 int sg_step(sg_handle h, const double *basal, const double *bolus, double *out, void *stream);
 
+/* Same as sg_step, with the meal announcements of this step supplied by the caller instead of the meal
+ * table: meals [sample_time][E] = scenario.get_action(time).meal for each minute of the step (env.py:50).
+ * This is the seam for arbitrary Scenario subclasses (simulation/scenario.py:10-21) evaluated on the host. */
+int sg_step_meals(sg_handle h, const double *basal, const double *bolus, const double *meals, double *out,
+                  void *stream);
+
+/* Replaces the buffers borrowed by sg_reset without resetting the episodes (longer noise stream / meal
+ * table as an open-ended episode proceeds).  Positions already consumed stay valid. */
+int sg_rebind_streams(sg_handle h, const int32_t *meal_minute, const double *meal_grams, int32_t max_meals,
+                      const double *noise, int64_t n_noise);
+
+/* patient.t at reset: T1DPatient(..., t0=...) (patient/t1dpatient.py:27,277).  Default 0. */
+int sg_set_t0(sg_handle h, int32_t t0);
+
+/* T1DPatient.step (patient/t1dpatient.py:82-116) for every episode: meal state machine + one minute of
+ * dopri5 with an explicit patient Action(CHO = grams announced this minute, insulin U/min).
+ * out [SG_NPOUT][E] (may be NULL): x[13], Gsub (observation, t1dpatient.py:210-220), grams eaten this
+ * minute, idid of this call, DOPRI5 steps taken. */
+#define SG_NPOUT 17
+int sg_patient_step(sg_handle h, const double *cho, const double *insulin, double *out, void *stream);
+
+/* T1DPatient.model (patient/t1dpatient.py:118-208): dxdt [SG_NX][n] for n independent evaluations.
+ * x [SG_NX][n]; cho, insulin, last_qsto, last_food [n]; parameters from params_soa [SG_NPARAM][n] or,
+ * when NULL, from the loaded table by patient_row [n]. */
+int sg_model(sg_handle h, int64_t n, const double *x, const double *cho, const double *insulin,
+             const double *last_qsto, const double *last_food, const int32_t *patient_row,
+             const double *params_soa, double *dxdt, void *stream);
+
+/* InsulinPump.basal / .bolus (actuator/pump.py:23-39), elementwise on the current device. */
+int sg_pump(const double *amount, double *out, int64_t n, double vmin, double vmax, double inc, void *stream);
+
+/* risk_index([BG], 1) (analysis/risk.py:5-17), elementwise: out [3][n] = LBGI, HBGI, RI. */
+int sg_risk_index(const double *bg, double *out, int64_t n, void *stream);
+
 /* SimObj.simulate (simulation/sim_engine.py:29-39) for every episode, n_steps env-steps fused in
  * one launch with the controller evaluated on device.
  *   ctrl_host [SG_NCTRL]      controller constants used for every episode when ctrl_rows is NULL
@@ -167,6 +201,11 @@ int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const i
 
 /* out[i] ~ U(lo, hi): random basal actions (BASELINE.json configs[2]). */
 int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, uint64_t offset, void *stream);
+
+/* Accuracy probe of the kernel's own FP64 helpers (csrc/sg_math.cuh) against CUDA's libm, elementwise:
+ * kind 0 div_nr(a,b), 1 a/b, 2 tanh_diff(a,b), 3 tanh(a)-tanh(b), 4 pow_pos(a,b), 5 pow(a,b), 6 exp_core(a),
+ * 7 exp(a), 8 log_core(a), 9 log(a).  Test hook only. */
+int sg_math_probe(int32_t kind, const double *a, const double *b, double *out, int64_t n, void *stream);
 
 /* FP64 pipe probe: n_blocks x n_threads threads each run `iters` x 8 independent DFMA; out gets one double per
  * thread.  Flops = n_blocks * n_threads * iters * 16.  bench.py times it for the roofline denominator. */

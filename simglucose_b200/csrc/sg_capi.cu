@@ -10,6 +10,8 @@
 static_assert(SG_NTRACE == sgk::NTRACE, "trace columns");
 static_assert(SG_NSTAT == sgk::NSTAT, "stat columns");
 static_assert(SG_NCTRL == sgk::NCTRL, "controller constants");
+static_assert(SG_NPOUT == sgk::NPOUT, "patient step rows");
+static_assert(SG_NPARAM == 32 && SG_NX == 13, "table shapes");
 
 namespace {
 
@@ -47,6 +49,7 @@ struct sg_context {
     int64_t n_noise = 0;
     int64_t steps_done = 0;
     bool is_reset = false;
+    int32_t t0 = 0;
     int64_t launches = 0;
 };
 
@@ -169,7 +172,7 @@ int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const 
     h->noise = noise; h->n_noise = n_noise;
     h->steps_done = 0;
     sgk::EpisodeArgs a = base_args(h);
-    a.x0 = x0; a.row0 = row0;
+    a.x0 = x0; a.row0 = row0; a.t0 = h->t0;
     cudaError_t ce = use_fma(h) ? sg_fma::launch_reset(a, (cudaStream_t)stream)
                                 : sg_strict::launch_reset(a, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_reset: launch", ce);
@@ -180,7 +183,8 @@ int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const 
 
 static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, const double *ctrl_rows,
                     const double *basal, const double *bolus, int64_t act_stride, int32_t n_steps,
-                    double *trace, int32_t *counters, void *stream, const char *who)
+                    double *trace, int32_t *counters, void *stream, const char *who,
+                    const double *step_meals = nullptr)
 {
     if (!h->is_reset) return fail(SG_ERR_STATE, who);
     if (h->steps_done + n_steps + 2 > h->n_noise) return fail(SG_ERR_ARG, "noise stream too short for the requested steps");
@@ -192,7 +196,7 @@ static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, co
     a.ctrl_rows = ctrl_rows;
     a.act_basal = basal; a.act_bolus = bolus; a.act_stride = act_stride;
     a.n_steps = n_steps;
-    a.trace = trace; a.counters = counters;
+    a.trace = trace; a.counters = counters; a.step_meals = step_meals;
     cudaError_t ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream)
                                 : sg_strict::launch_run(a, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
@@ -218,6 +222,93 @@ int sg_step(sg_handle h, const double *basal, const double *bolus, double *out, 
     if (!h) return fail(SG_ERR_ARG, "sg_step: null handle");
     if (!basal || !bolus) return fail(SG_ERR_ARG, "sg_step: basal and bolus required");
     return run_impl(h, SG_CTRL_ACTIONS, nullptr, nullptr, basal, bolus, 0, 1, out, nullptr, stream, "sg_step");
+}
+
+int sg_step_meals(sg_handle h, const double *basal, const double *bolus, const double *meals, double *out,
+                  void *stream)
+{
+    if (!h) return fail(SG_ERR_ARG, "sg_step_meals: null handle");
+    if (!basal || !bolus || !meals) return fail(SG_ERR_ARG, "sg_step_meals: basal, bolus and meals required");
+    return run_impl(h, SG_CTRL_ACTIONS, nullptr, nullptr, basal, bolus, 0, 1, out, nullptr, stream,
+                    "sg_step_meals", meals);
+}
+
+int sg_rebind_streams(sg_handle h, const int32_t *meal_minute, const double *meal_grams, int32_t max_meals,
+                      const double *noise, int64_t n_noise)
+{
+    if (!h) return fail(SG_ERR_ARG, "sg_rebind_streams: null handle");
+    if (!h->is_reset) return fail(SG_ERR_STATE, "sg_rebind_streams: call sg_reset first");
+    if (max_meals < 0 || (max_meals > 0 && (!meal_minute || !meal_grams))) return fail(SG_ERR_ARG, "sg_rebind_streams: meal table");
+    if (!noise || n_noise < h->steps_done + 2) return fail(SG_ERR_ARG, "sg_rebind_streams: noise stream shorter than what was consumed");
+    h->meal_minute = meal_minute; h->meal_grams = meal_grams; h->max_meals = max_meals;
+    h->noise = noise; h->n_noise = n_noise;
+    return SG_OK;
+}
+
+int sg_set_t0(sg_handle h, int32_t t0)
+{
+    if (!h || t0 < 0) return fail(SG_ERR_ARG, "sg_set_t0: bad arguments");
+    h->t0 = t0;
+    return SG_OK;
+}
+
+int sg_patient_step(sg_handle h, const double *cho, const double *insulin, double *out, void *stream)
+{
+    if (!h || !cho || !insulin) return fail(SG_ERR_ARG, "sg_patient_step: bad arguments");
+    if (!h->is_reset) return fail(SG_ERR_STATE, "sg_patient_step: call sg_reset first");
+    DeviceGuard g(h->device);
+    sgk::PatientArgs pa{};
+    pa.e = base_args(h);
+    pa.cho = cho; pa.insulin = insulin; pa.out = out;
+    cudaError_t ce = use_fma(h) ? sg_fma::launch_patient_step(pa, (cudaStream_t)stream)
+                                : sg_strict::launch_patient_step(pa, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_patient_step: launch", ce);
+    h->launches++;
+    return SG_OK;
+}
+
+int sg_model(sg_handle h, int64_t n, const double *x, const double *cho, const double *insulin,
+             const double *last_qsto, const double *last_food, const int32_t *patient_row,
+             const double *params_soa, double *dxdt, void *stream)
+{
+    if (!h || n <= 0 || !x || !cho || !insulin || !last_qsto || !last_food || !dxdt)
+        return fail(SG_ERR_ARG, "sg_model: bad arguments");
+    if (!params_soa && (!patient_row || !h->table)) return fail(SG_ERR_ARG, "sg_model: need params_soa, or patient_row + sg_load_params");
+    DeviceGuard g(h->device);
+    sgk::ModelArgs m{};
+    m.n = n; m.x = x; m.cho = cho; m.insulin = insulin; m.last_qsto = last_qsto; m.last_food = last_food;
+    m.params_soa = params_soa; m.table = h->table; m.patient_row = patient_row; m.dxdt = dxdt;
+    cudaError_t ce = use_fma(h) ? sg_fma::launch_model(m, (cudaStream_t)stream)
+                                : sg_strict::launch_model(m, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_model: launch", ce);
+    h->launches++;
+    return SG_OK;
+}
+
+int sg_pump(const double *amount, double *out, int64_t n, double vmin, double vmax, double inc, void *stream)
+{
+    if (!amount || !out || n <= 0 || !(inc > 0.0)) return fail(SG_ERR_ARG, "sg_pump: bad arguments");
+    sgk::ElementwiseArgs a{n, amount, out, {vmin, vmax, inc}};
+    cudaError_t ce = sg_strict::launch_pump(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_pump: launch", ce);
+    return SG_OK;
+}
+
+int sg_risk_index(const double *bg, double *out, int64_t n, void *stream)
+{
+    if (!bg || !out || n <= 0) return fail(SG_ERR_ARG, "sg_risk_index: bad arguments");
+    sgk::ElementwiseArgs a{n, bg, out, {0.0, 0.0, 0.0}};
+    cudaError_t ce = sg_strict::launch_risk(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_risk_index: launch", ce);
+    return SG_OK;
+}
+
+int sg_math_probe(int32_t kind, const double *a, const double *b, double *out, int64_t n, void *stream)
+{
+    if (kind < 0 || kind > 9 || !a || !b || !out || n <= 0) return fail(SG_ERR_ARG, "sg_math_probe: bad arguments");
+    cudaError_t ce = sg_strict::launch_math_probe(kind, a, b, out, n, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_math_probe: launch", ce);
+    return SG_OK;
 }
 
 static int copy_out(sg_handle h, void *dst, const void *src, size_t elem, int rows, void *stream, const char *who)

@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
     sd[(int64_t)SD_PID_INTEG * a.cap] = 0.0;                // controller.reset(), pid_ctrller.py:38-40
     sd[(int64_t)SD_PID_PREV * a.cap] = 0.0;
     si[(int64_t)SI_EATING * a.cap] = 0;
-    si[(int64_t)SI_MINUTE * a.cap] = 0;
+    si[(int64_t)SI_MINUTE * a.cap] = a.t0;
     si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
     si[(int64_t)SI_MEAL_POS * a.cap] = 0;
     si[(int64_t)SI_STATUS * a.cap] = 1;
@@ -186,11 +186,15 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
         double CHO = 0.0, insulin = 0.0, BG = 0.0, CGM = 0.0;
         for (int j = 0; j < st_i; j++) {               // mini_step, env.py:48-64
             double announced = 0.0;
-            while (next_mm >= 0 && next_mm < minute) {
-                meal_pos++;
-                next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+            if (a.step_meals) {                        // scenario.get_action evaluated by the caller
+                announced = a.step_meals[(int64_t)j * a.n + e];
+            } else {
+                while (next_mm >= 0 && next_mm < minute) {
+                    meal_pos++;
+                    next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+                }
+                if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
             }
-            if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
             const double to_eat = meal_machine(meal, announced, x[0], x[1]);
             const Minute m = minute_setup(c, to_eat, ins, meal.last_Qsto, meal.last_food);
             StepCount cnt{0, 0};
@@ -244,6 +248,117 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     si[(int64_t)SI_STATUS * a.cap] = status;
 #pragma unroll
     for (int i = 0; i < NSTAT; i++) a.stats[(int64_t)i * a.cap + e] = s[i];
+}
+
+// T1DPatient.step (t1dpatient.py:82-116) for every episode: the patient-level seam of the reference
+// (an env built from user-supplied sensor / pump / scenario objects drives the patient minute by minute).
+__global__ void __launch_bounds__(BLOCK) patient_step_kernel(const PatientArgs pa)
+{
+    extern __shared__ double smem[];
+    const EpisodeArgs &a = pa.e;
+    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (e >= a.n) return;
+    const Column<BLOCK> c{smem + threadIdx.x};
+    const ParamLoad p = param_source(a, e);
+    stage_params(c, p);
+    double *sd = a.sd + e;
+    int32_t *si = a.si + e;
+    double x[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) x[i] = sd[(int64_t)(SD_X0 + i) * a.cap];
+    Meal meal;
+    meal.planned = sd[(int64_t)SD_PLANNED * a.cap];
+    meal.last_cho = sd[(int64_t)SD_LAST_CHO * a.cap];
+    meal.last_Qsto = sd[(int64_t)SD_LAST_QSTO * a.cap];
+    meal.last_food = sd[(int64_t)SD_LAST_FOOD * a.cap];
+    meal.eating = si[(int64_t)SI_EATING * a.cap];
+    double h_carry = sd[(int64_t)SD_H_CARRY * a.cap];
+    int minute = si[(int64_t)SI_MINUTE * a.cap];
+    int status = si[(int64_t)SI_STATUS * a.cap];
+
+    const double to_eat = meal_machine(meal, pa.cho[e], x[0], x[1]);
+    const Minute m = minute_setup(c, to_eat, pa.insulin[e], meal.last_Qsto, meal.last_food);
+    StepCount cnt{0, 0};
+    const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt);
+    if (idid < 0 && status > 0) status = idid;
+    minute++;
+
+#pragma unroll
+    for (int i = 0; i < NX; i++) sd[(int64_t)(SD_X0 + i) * a.cap] = x[i];
+    sd[(int64_t)SD_PLANNED * a.cap] = meal.planned;
+    sd[(int64_t)SD_LAST_CHO * a.cap] = meal.last_cho;
+    sd[(int64_t)SD_LAST_QSTO * a.cap] = meal.last_Qsto;
+    sd[(int64_t)SD_LAST_FOOD * a.cap] = meal.last_food;
+    sd[(int64_t)SD_H_CARRY * a.cap] = h_carry;
+    si[(int64_t)SI_EATING * a.cap] = meal.eating;
+    si[(int64_t)SI_MINUTE * a.cap] = minute;
+    si[(int64_t)SI_STATUS * a.cap] = status;
+    if (pa.out) {
+        double *o = pa.out + e;
+#pragma unroll
+        for (int i = 0; i < NX; i++) o[(int64_t)i * a.n] = x[i];
+        o[(int64_t)13 * a.n] = x[12] / c(H_Vg);                 // observation.Gsub, t1dpatient.py:217-218
+        o[(int64_t)14 * a.n] = to_eat;
+        o[(int64_t)15 * a.n] = (double)idid;
+        o[(int64_t)16 * a.n] = (double)cnt.nstep;
+    }
+}
+
+// T1DPatient.model (t1dpatient.py:118-208) as a batched function evaluation.
+__global__ void __launch_bounds__(BLOCK) model_kernel(const ModelArgs a)
+{
+    extern __shared__ double smem[];
+    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    if (e >= a.n) return;
+    const Column<BLOCK> c{smem + threadIdx.x};
+    const ParamLoad p = a.params_soa ? ParamLoad{a.params_soa + e, a.n}
+                                     : ParamLoad{a.table + (int64_t)a.patient_row[e] * P_COUNT, 1};
+    stage_params(c, p);
+    double x[NX], dx[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) x[i] = a.x[(int64_t)i * a.n + e];
+    const Minute m = minute_setup(c, a.cho[e], a.insulin[e], a.last_qsto[e], a.last_food[e]);
+    rhs(c, m, x, dx);
+#pragma unroll
+    for (int i = 0; i < NX; i++) a.dxdt[(int64_t)i * a.n + e] = dx[i];
+}
+
+// InsulinPump.basal / .bolus (pump.py:23-39) and risk_index([BG], 1) (risk.py:5-17), elementwise.
+__global__ void __launch_bounds__(256) pump_kernel(const ElementwiseArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i < a.n) a.out[i] = pump_quantise(a.in[i], a.p[0], a.p[1], a.p[2]);
+}
+
+__global__ void __launch_bounds__(256) risk_kernel(const ElementwiseArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= a.n) return;
+    double l, h, r;
+    risk_index(a.in[i], l, h, r);
+    a.out[i] = l; a.out[a.n + i] = h; a.out[2 * a.n + i] = r;
+}
+
+// Accuracy probe of the helpers in sg_math.cuh against CUDA's libm (tests/test_gpu_math.py).
+__global__ void __launch_bounds__(256) math_probe_kernel(int kind, const double *a, const double *b, double *out, int64_t n)
+{
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const double u = a[i], v = b[i];
+    double r;
+    switch (kind) {
+    case 0: r = sgm::div_nr(u, v); break;
+    case 1: r = u / v; break;
+    case 2: r = sgm::tanh_diff(u, v); break;
+    case 3: r = tanh(u) - tanh(v); break;
+    case 4: r = sgm::pow_pos(u, v); break;
+    case 5: r = pow(u, v); break;
+    case 6: r = sgm::exp_core(u); break;
+    case 7: r = exp(u); break;
+    case 8: r = sgm::log_core(u); break;
+    default: r = log(u); break;
+    }
+    out[i] = r;
 }
 
 // ---- population statistics ------------------------------------------------------------------
@@ -321,6 +436,50 @@ cudaError_t launch_run(const EpisodeArgs &a, cudaStream_t s)
         configured = true;
     }
     run_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_patient_step(const PatientArgs &a, cudaStream_t s)
+{
+    constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(patient_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    patient_step_kernel<<<grid_for(a.e.n), BLOCK, kSmem, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_model(const ModelArgs &a, cudaStream_t s)
+{
+    constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(model_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    model_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pump(const ElementwiseArgs &a, cudaStream_t s)
+{
+    pump_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_risk(const ElementwiseArgs &a, cudaStream_t s)
+{
+    risk_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_math_probe(int kind, const double *a, const double *b, double *out, int64_t n, cudaStream_t s)
+{
+    math_probe_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(kind, a, b, out, n);
     return cudaGetLastError();
 }
 

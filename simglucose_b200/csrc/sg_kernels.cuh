@@ -69,11 +69,40 @@ struct EpisodeArgs {
     const double *act_bolus;
     int64_t act_stride;
     int32_t n_steps;
+    const double *step_meals;  // [st][n] grams announced in each minute of a single step (n_steps == 1), or null: table
     double *trace;             // [n_steps][NTRACE][n] or null
     int32_t *counters;         // [n_steps*st][2][n] or null
     // reset
     const double *x0;          // [13][n] or null
     double *row0;              // [NTRACE][n] or null
+    int32_t t0;                // patient.t at reset (T1DPatient(t0=...), t1dpatient.py:27,277)
+};
+
+// T1DPatient.step for every episode: one minute with an explicit Action(CHO announced, insulin).
+constexpr int NPOUT = 17;      // out rows: x[13], Gsub, to_eat, idid, dopri5 steps
+struct PatientArgs {
+    EpisodeArgs e;
+    const double *cho;         // [n] grams announced this minute
+    const double *insulin;     // [n] U/min
+    double *out;               // [NPOUT][n] or null
+};
+
+// T1DPatient.model evaluated for n independent (x, action, last_Qsto, last_foodtaken).
+struct ModelArgs {
+    int64_t n;
+    const double *x;           // [13][n]
+    const double *cho, *insulin, *last_qsto, *last_food;   // [n]
+    const double *params_soa;  // [32][n] or null
+    const double *table;
+    const int32_t *patient_row;
+    double *dxdt;              // [13][n]
+};
+
+struct ElementwiseArgs {
+    int64_t n;
+    const double *in;
+    double *out;
+    double p[3];
 };
 
 struct ReduceArgs {
@@ -89,6 +118,11 @@ struct ReduceArgs {
     cudaError_t launch_reset(const sgk::EpisodeArgs &a, cudaStream_t s);      \
     cudaError_t launch_run(const sgk::EpisodeArgs &a, cudaStream_t s);        \
     cudaError_t launch_reduce(const sgk::ReduceArgs &a, cudaStream_t s);      \
+    cudaError_t launch_patient_step(const sgk::PatientArgs &a, cudaStream_t s); \
+    cudaError_t launch_model(const sgk::ModelArgs &a, cudaStream_t s);        \
+    cudaError_t launch_pump(const sgk::ElementwiseArgs &a, cudaStream_t s);   \
+    cudaError_t launch_risk(const sgk::ElementwiseArgs &a, cudaStream_t s);   \
+    cudaError_t launch_math_probe(int kind, const double *a, const double *b, double *out, int64_t n, cudaStream_t s); \
     int reduce_blocks(int64_t n);                                             \
     }
 

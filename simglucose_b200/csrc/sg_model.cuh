@@ -21,6 +21,8 @@
 #include <cmath>
 #include <cstdint>
 
+#include "sg_math.cuh"
+
 namespace sgk {
 
 constexpr int NX = 13;
@@ -32,10 +34,7 @@ enum Hoisted {
     H_Ib, H_ki, H_m13, H_m2, H_kad, H_kd, H_ksc, H_Vg,
     // per-minute values (rewritten by the owning thread at every minute start)
     H_aa, H_cc, H_bD, H_dD,
-    // scratch rows: the 13-component error / HINIT norms run as rolled loops over this staging area so
-    // that each IEEE division is emitted once instead of 13 times (instruction-cache footprint)
-    H_SCRATCH,
-    H_COUNT = H_SCRATCH + 2 * NX
+    H_COUNT
 };
 
 // Order of the parameter row handed over the C-ABI (include/simglucose_b200.h, sg_param).
@@ -49,7 +48,9 @@ enum Param {
 template <int BLOCK>
 struct Column {
     double *base;   // &smem[threadIdx.x]
-    __device__ __forceinline__ double operator()(int i) const { return base[i * BLOCK]; }
+    // volatile: every use re-reads shared memory.  Without it ptxas keeps the ~35 parameters of the eight
+    // inlined RHS copies in registers and spills Runge-Kutta stages to local memory instead.
+    __device__ __forceinline__ double operator()(int i) const { return ((const volatile double *)base)[i * BLOCK]; }
     __device__ __forceinline__ void set(int i, double v) const { base[i * BLOCK] = v; }
 };
 
@@ -116,16 +117,16 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     dx[0] = -kmax * x[0] + m.d;                                             // :133
     double kgut;
     if (m.fed) {                                                            // :135-142
-        const double ta = tanh(c(H_aa) * (qsto - c(H_bD)));
-        const double tc = tanh(c(H_cc) * (qsto - c(H_dD)));
-        kgut = c(H_kmin) + c(H_hk) * (ta - tc + 2.0);
+        // tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh)
+        const double tdiff = sgm::tanh_diff(c(H_aa) * (qsto - c(H_bD)), c(H_cc) * (qsto - c(H_dD)));
+        kgut = c(H_kmin) + c(H_hk) * (tdiff + 2.0);
     } else {
         kgut = kmax;
     }
     dx[1] = kmax * x[0] - x[1] * kgut;                                      // :145
     const double kabs = c(H_kabs);
     dx[2] = kgut * x[1] - kabs * x[2];                                      // :148
-    const double Rat = c(H_fk) * x[2] / c(H_BW);                            // :151
+    const double Rat = sgm::div_nr(c(H_fk) * x[2], c(H_BW));                            // :151
     const double EGPt = c(H_kp1) - c(H_kp2) * x[3] - c(H_kp3) * x[8];       // :153
     const double ke2 = c(H_ke2);
     const double Et = (x[3] > ke2) ? c(H_ke1) * (x[3] - ke2) : 0.0;         // :158-161
@@ -133,11 +134,11 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     const double k1 = c(H_k1), k2 = c(H_k2);
     dx[3] = mask_nonneg(x[3], egp + Rat - c(H_Fsnc) - Et - k1 * x[3] + k2 * x[4]);   // :165-167
     const double Vmt = c(H_Vm0) + c(H_Vmx) * x[6];                          // :169
-    const double Uidt = Vmt * x[4] / (c(H_Km0) + x[4]);                     // :171
+    const double Uidt = sgm::div_nr(Vmt * x[4], c(H_Km0) + x[4]);                     // :171
     dx[4] = mask_nonneg(x[4], -Uidt + k1 * x[3] - k2 * x[4]);               // :172-173
     const double ka2 = c(H_ka2), m2 = c(H_m2);
     dx[5] = mask_nonneg(x[5], -c(H_m24) * x[5] + c(H_m1) * x[9] + c(H_ka1) * x[10] + ka2 * x[11]);
-    const double It = x[5] / c(H_Vi);                                       // :178
+    const double It = sgm::div_nr(x[5], c(H_Vi));                                       // :178
     const double p2u = c(H_p2u), ki = c(H_ki);
     dx[6] = -p2u * x[6] + p2u * (It - c(H_Ib));                             // :182
     dx[7] = -ki * (x[7] - It);                                              // :185
@@ -251,10 +252,10 @@ struct StepCount { int nstep, nrej; };
 // size is carried over, then the adaptive step loop.  Returns idid (1 ok, -2 nmax, -3 step too small).
 // h_carry: WORK(7) of the Fortran (kept across calls by scipy 1.6.3, zero in scipy >= 1.7).
 //
-// Written as a phase machine around ONE instance of the RHS: phase 0 evaluates k1, phase 1 the HINIT
-// probe f(y + h*k1), phases 2..7 the stages k2..k7.  Eight inlined copies of the RHS (two tanh each)
-// made a 140 KB kernel that stalled on instruction fetch (profiles/r01_*); this form is ~4x smaller.
-// All lanes of a warp walk the phases together, so the switches are uniform branches.
+// Straight-line form: every stage has its own inlined copy of the RHS, so the stage vectors never move
+// between registers and ptxas can overlap the tail of one stage with the linear combinations of the next.
+// The RHS copies are small (custom exp/division, sg_math.cuh); the step body is one basic block apart
+// from the uniform `fed` test.
 template <int BLOCK>
 __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minute &m, double (&y)[NX],
                                              double t0, bool carry_h, double &h_carry, StepCount &cnt)
@@ -267,169 +268,97 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     const double hmax = fabs(xend - x);
     double facold = 1.0e-4;
     bool last = false, reject = false;
-    int nstep = 0, naccpt = 0, idid = 0, phase = 0;
-    double k1[NX], k2[NX], k3[NX], k4[NX], k5[NX], k6[NX], yt[NX], kt[NX];
-    double h = 0.0, dnf = 0.0;
+    int nstep = 0, naccpt = 0, idid = 0;
+    double k1[NX], k2[NX], k3[NX], k4[NX], k5[NX], k6[NX], yt[NX];
+
+    rhs(c, m, y, k1);
+    double h = carry_h ? h_carry : 0.0;
+    if (h == 0.0) {                                          // HINIT
+        double dnf = 0.0, dny = 0.0;
+#pragma unroll
+        for (int i = 0; i < NX; i++) {
+            const double sk = ATOL + RTOL * fabs(y[i]);
+            const double a = sgm::div_nr(k1[i], sk), b = sgm::div_nr(y[i], sk);
+            dnf = dnf + a * a;
+            dny = dny + b * b;
+        }
+        h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+        h = fmin(h, hmax);
+#pragma unroll
+        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * k1[i];
+        rhs(c, m, yt, k2);
+        double der2 = 0.0;
+#pragma unroll
+        for (int i = 0; i < NX; i++) {
+            const double sk = ATOL + RTOL * fabs(y[i]);
+            const double a = sgm::div_nr(k2[i] - k1[i], sk);
+            der2 = der2 + a * a;
+        }
+        der2 = sqrt(der2) / h;
+        const double der12 = fmax(fabs(der2), sqrt(dnf));
+        const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
+        h = fmin(fmin(100.0 * fabs(h), h1), hmax);
+    }
 
 #pragma unroll 1
-    while (idid == 0) {
-        switch (phase) {
-        case 0:
+    for (;;) {
+        if (nstep > NMAX) { idid = -2; break; }
+        if (0.1 * fabs(h) <= fabs(x) * UROUND) { idid = -3; break; }
+        if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
+        nstep++;
+        {
+            const double ha = h * A21;
 #pragma unroll
-            for (int i = 0; i < NX; i++) yt[i] = y[i];
-            break;
-        case 1:
-#pragma unroll
-            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * k1[i];
-            break;
-        case 2:
-#pragma unroll
-            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * A21 * k1[i];
-            break;
-        case 3:
-#pragma unroll
-            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A31 * k1[i] + A32 * k2[i]);
-            break;
-        case 4:
-#pragma unroll
-            for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A41 * k1[i] + A42 * k2[i] + A43 * k3[i]);
-            break;
-        case 5:
-#pragma unroll
-            for (int i = 0; i < NX; i++)
-                yt[i] = y[i] + h * (A51 * k1[i] + A52 * k2[i] + A53 * k3[i] + A54 * k4[i]);
-            break;
-        case 6:
-#pragma unroll
-            for (int i = 0; i < NX; i++)
-                yt[i] = y[i] + h * (A61 * k1[i] + A62 * k2[i] + A63 * k3[i] + A64 * k4[i] + A65 * k5[i]);
-            break;
-        default:
-#pragma unroll
-            for (int i = 0; i < NX; i++)
-                yt[i] = y[i] + h * (A71 * k1[i] + A73 * k3[i] + A74 * k4[i] + A75 * k5[i] + A76 * k6[i]);
-            break;
+            for (int i = 0; i < NX; i++) yt[i] = y[i] + ha * k1[i];
         }
-
-        rhs(c, m, yt, kt);
-
-        bool begin_step = false;
-        switch (phase) {
-        case 0: {
+        rhs(c, m, yt, k2);
 #pragma unroll
-            for (int i = 0; i < NX; i++) k1[i] = kt[i];
-            h = carry_h ? h_carry : 0.0;
-            if (h == 0.0) {                                  // HINIT, first half
-                double dny = 0.0;
-                dnf = 0.0;
+        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A31 * k1[i] + A32 * k2[i]);
+        rhs(c, m, yt, k3);
 #pragma unroll
-                for (int i = 0; i < NX; i++) { c.set(H_SCRATCH + i, y[i]); c.set(H_SCRATCH + NX + i, k1[i]); }
-#pragma unroll 1
-                for (int i = 0; i < NX; i++) {
-                    const double yi = c(H_SCRATCH + i);
-                    const double sk = ATOL + RTOL * fabs(yi);
-                    const double a = c(H_SCRATCH + NX + i) / sk, b = yi / sk;
-                    dnf = dnf + a * a;
-                    dny = dny + b * b;
-                }
-                h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
-                h = fmin(h, hmax);
-                phase = 1;
-            } else {
-                begin_step = true;
-            }
-        } break;
-        case 1: {                                            // HINIT, second half: kt = f(x + h, y + h*k1)
-            double der2 = 0.0;
+        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A41 * k1[i] + A42 * k2[i] + A43 * k3[i]);
+        rhs(c, m, yt, k4);
 #pragma unroll
-            for (int i = 0; i < NX; i++) { c.set(H_SCRATCH + i, y[i]); c.set(H_SCRATCH + NX + i, kt[i] - k1[i]); }
-#pragma unroll 1
-            for (int i = 0; i < NX; i++) {
-                const double sk = ATOL + RTOL * fabs(c(H_SCRATCH + i));
-                const double a = c(H_SCRATCH + NX + i) / sk;
-                der2 = der2 + a * a;
-            }
-            der2 = sqrt(der2) / h;
-            const double der12 = fmax(fabs(der2), sqrt(dnf));
-            const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : pow(0.01 / der12, 1.0 / 5.0);
-            h = fmin(fmin(100.0 * fabs(h), h1), hmax);
-            begin_step = true;
-        } break;
-        case 2:
+        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A51 * k1[i] + A52 * k2[i] + A53 * k3[i] + A54 * k4[i]);
+        rhs(c, m, yt, k5);
 #pragma unroll
-            for (int i = 0; i < NX; i++) k2[i] = kt[i];
-            phase = 3;
-            break;
-        case 3:
+        for (int i = 0; i < NX; i++)
+            yt[i] = y[i] + h * (A61 * k1[i] + A62 * k2[i] + A63 * k3[i] + A64 * k4[i] + A65 * k5[i]);
+        rhs(c, m, yt, k6);
 #pragma unroll
-            for (int i = 0; i < NX; i++) k3[i] = kt[i];
-            phase = 4;
-            break;
-        case 4:
+        for (int i = 0; i < NX; i++)
+            yt[i] = y[i] + h * (A71 * k1[i] + A73 * k3[i] + A74 * k4[i] + A75 * k5[i] + A76 * k6[i]);
+        rhs(c, m, yt, k2);                                   // k7 = f(x + h, y1), kept in k2 (FSAL)
+        double err = 0.0;
 #pragma unroll
-            for (int i = 0; i < NX; i++) k4[i] = kt[i];
-            phase = 5;
-            break;
-        case 5:
-#pragma unroll
-            for (int i = 0; i < NX; i++) k5[i] = kt[i];
-            phase = 6;
-            break;
-        case 6:
-#pragma unroll
-            for (int i = 0; i < NX; i++) k6[i] = kt[i];
-            phase = 7;
-            break;
-        default: {                                           // kt = k7 = f(x + h, y1): error estimate + control
-            double err = 0.0;
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                c.set(H_SCRATCH + i, (E1 * k1[i] + E3 * k3[i] + E4 * k4[i] + E5 * k5[i] + E6 * k6[i] + E7 * kt[i]) * h);
-                c.set(H_SCRATCH + NX + i, ATOL + RTOL * fmax(fabs(y[i]), fabs(yt[i])));
-            }
-#pragma unroll 1
-            for (int i = 0; i < NX; i++) {
-                const double a = c(H_SCRATCH + i) / c(H_SCRATCH + NX + i);
-                err = err + a * a;
-            }
-            err = sqrt(err / (double)NX);
-            const double fac11 = pow(err, expo1);
-            double fac = fac11 / pow(facold, beta);
-            fac = fmax(facc2, fmin(facc1, fac / safe));
-            double hnew = h / fac;
-            if (err <= 1.0) {
-                facold = fmax(err, 1.0e-4);
-                naccpt++;
-#pragma unroll
-                for (int i = 0; i < NX; i++) { k1[i] = kt[i]; y[i] = yt[i]; }   // FSAL
-                x = x + h;
-                if (last) {
-                    idid = 1;
-                } else {
-                    if (fabs(hnew) > hmax) hnew = hmax;
-                    if (reject) hnew = fmin(fabs(hnew), fabs(h));
-                    reject = false;
-                    begin_step = true;
-                }
-            } else {
-                hnew = h / fmin(facc1, fac11 / safe);
-                reject = true;
-                if (naccpt >= 1) cnt.nrej++;
-                last = false;
-                begin_step = true;
-            }
-            h = hnew;
-        } break;
+        for (int i = 0; i < NX; i++) {
+            const double e = (E1 * k1[i] + E3 * k3[i] + E4 * k4[i] + E5 * k5[i] + E6 * k6[i] + E7 * k2[i]) * h;
+            const double sk = ATOL + RTOL * fmax(fabs(y[i]), fabs(yt[i]));
+            const double a = sgm::div_nr(e, sk);
+            err = err + a * a;
         }
-        if (begin_step) {
-            if (nstep > NMAX) idid = -2;
-            else if (0.1 * fabs(h) <= fabs(x) * UROUND) idid = -3;
-            else {
-                if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
-                nstep++;
-                phase = 2;
-            }
+        err = sqrt(err / (double)NX);
+        const double fac11 = sgm::pow_pos(err, expo1);
+        double fac = fac11 / sgm::pow_pos(facold, beta);
+        fac = fmax(facc2, fmin(facc1, fac / safe));
+        double hnew = h / fac;
+        if (err <= 1.0) {
+            facold = fmax(err, 1.0e-4);
+            naccpt++;
+#pragma unroll
+            for (int i = 0; i < NX; i++) { k1[i] = k2[i]; y[i] = yt[i]; }
+            x = x + h;
+            if (last) { h = hnew; idid = 1; break; }
+            if (fabs(hnew) > hmax) hnew = hmax;
+            if (reject) hnew = fmin(fabs(hnew), fabs(h));
+            reject = false;
+        } else {
+            hnew = h / fmin(facc1, fac11 / safe);
+            reject = true;
+            if (naccpt >= 1) cnt.nrej++;
+            last = false;
         }
+        h = hnew;
     }
     if (carry_h) h_carry = h;
     cnt.nstep += nstep;

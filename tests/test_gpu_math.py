@@ -1,0 +1,80 @@
+"""The kernels' own FP64 helpers (csrc/sg_math.cuh) against CUDA's libm, on the GPU, through the C-ABI test
+hook sg_math_probe.  div_nr must reproduce IEEE division bit for bit in the range the kernels use it."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _probe(kind, a, b):
+    import torch
+    from simglucose_b200 import _capi
+    lib = _capi.load()
+    ta = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).cuda()
+    tb = torch.from_numpy(np.ascontiguousarray(b, dtype=np.float64)).cuda()
+    out = torch.empty_like(ta)
+    _capi.check(lib.sg_math_probe(kind, C.c_void_p(ta.data_ptr()), C.c_void_p(tb.data_ptr()),
+                                  C.c_void_p(out.data_ptr()), ta.numel(),
+                                  C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def test_div_nr_is_ieee_division_bit_for_bit():
+    rng = np.random.RandomState(0)
+    n = 1 << 22
+    # numerators over 500 decades (both signs, exact zeros), denominators like the kernels': tolerances
+    # (1e-12 .. 1e-3), body weights / volumes (1 .. 1e3), Km0 + x (1e2 .. 1e4)
+    a = np.exp(rng.uniform(-600.0, 300.0, n)) * rng.choice([-1.0, 1.0], n)
+    a[::97] = 0.0
+    b = np.exp(rng.uniform(np.log(1e-13), np.log(1e5), n))
+    got, ref = _probe(0, a, b), _probe(1, a, b)
+    big = np.abs(a) >= 2.0 ** -960
+    assert np.array_equal(got[big].view(np.int64), ref[big].view(np.int64))
+    assert np.array_equal(got[a == 0.0], ref[a == 0.0])
+    small = ~big & (a != 0.0)
+    assert np.all(np.abs(got[small] - ref[small]) <= np.abs(ref[small]) * 2.3e-16 + 5e-324)
+    # mantissa corner cases
+    m = np.array([1.0, 1.0 + 2.0 ** -52, 2.0 - 2.0 ** -52, 1.5, 4.0 / 3.0, 1.0 / 3.0, 0.1, 0.05, 6000.0, 1e-12, 1e-6])
+    aa, bb = np.meshgrid(m, m)
+    assert np.array_equal(_probe(0, aa.ravel(), bb.ravel()).view(np.int64), _probe(1, aa.ravel(), bb.ravel()).view(np.int64))
+
+
+def test_exp_log_within_one_ulp_of_libm():
+    rng = np.random.RandomState(1)
+    n = 1 << 20
+    t = rng.uniform(-160.0, 160.0, n)
+    got, ref = _probe(6, t, t), _probe(7, t, t)
+    assert np.max(np.abs(got - ref) / ref) <= 3.4e-16
+    x = np.exp(rng.uniform(-690.0, 690.0, n))
+    got, ref = _probe(8, x, x), _probe(9, x, x)
+    ok = np.abs(ref) > 1e-3
+    assert np.max(np.abs(got[ok] - ref[ok]) / np.abs(ref[ok])) <= 3.4e-16
+    assert np.max(np.abs(got - ref)) <= 1e-13
+
+
+def test_tanh_diff_absolute_error():
+    rng = np.random.RandomState(2)
+    n = 1 << 20
+    u = rng.uniform(-60.0, 5.0, n)      # aa * (qsto - b*Dbar): -2.5 b/(1-b) .. 2.5
+    v = rng.uniform(-5.0, 30.0, n)      # cc * (qsto - d*Dbar): -2.5 .. 2.5 (1-d)/d
+    got, ref = _probe(2, u, v), _probe(3, u, v)
+    assert np.max(np.abs(got - ref)) <= 1.2e-15
+    z = np.zeros(4)
+    assert np.array_equal(_probe(2, z, z), z)
+    big = np.array([1e300, -1e300, 700.0, -700.0])
+    assert np.array_equal(_probe(2, big, -big), np.array([2.0, -2.0, 2.0, -2.0]))
+
+
+def test_pow_pos_step_controller_exponents():
+    rng = np.random.RandomState(3)
+    n = 1 << 20
+    for y in (0.2 - 0.04 * 0.75, 0.04, 0.2):
+        x = np.exp(rng.uniform(-14.0, 14.0, n))      # err, facold, 0.01/der12 seen by the controller
+        got, ref = _probe(4, x, np.full(n, y)), _probe(5, x, np.full(n, y))
+        assert np.max(np.abs(got - ref) / ref) <= 6e-16
+    # clamps: 0 and inf behave like any value beyond the controller's limits (facc1 = 5, facc2 = 0.1)
+    edge = _probe(4, np.array([0.0, np.inf]), np.array([0.17, 0.17]))
+    assert edge[0] < 1e-3 and edge[1] > 1e3
