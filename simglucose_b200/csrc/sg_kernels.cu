@@ -119,6 +119,7 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
 {
     extern __shared__ double smem[];   // H_COUNT rows x BLOCK columns
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);   // the lanes that own an episode
     if (e >= a.n) return;          // no block-level synchronisation below: columns are private
     const Column<BLOCK> c{smem + threadIdx.x};
     const ParamLoad p = param_source(a, e);
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
             const double to_eat = meal_machine(meal, announced, x[0], x[1]);
             const Minute m = minute_setup(c, to_eat, ins, meal.last_Qsto, meal.last_food);
             StepCount cnt{0, 0};
-            const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt);
+            const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt, lanes);
             if (idid < 0 && status > 0) status = idid;
             if (a.counters) {
                 const int64_t row = (int64_t)(k * st_i + j) * 2;
@@ -257,6 +258,7 @@ __global__ void __launch_bounds__(BLOCK) patient_step_kernel(const PatientArgs p
     extern __shared__ double smem[];
     const EpisodeArgs &a = pa.e;
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);
     if (e >= a.n) return;
     const Column<BLOCK> c{smem + threadIdx.x};
     const ParamLoad p = param_source(a, e);
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(BLOCK) patient_step_kernel(const PatientArgs p
     const double to_eat = meal_machine(meal, pa.cho[e], x[0], x[1]);
     const Minute m = minute_setup(c, to_eat, pa.insulin[e], meal.last_Qsto, meal.last_food);
     StepCount cnt{0, 0};
-    const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt);
+    const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt, lanes);
     if (idid < 0 && status > 0) status = idid;
     minute++;
 

@@ -34,7 +34,12 @@ enum Hoisted {
     H_Ib, H_ki, H_m13, H_m2, H_kad, H_kd, H_ksc, H_Vg,
     // per-minute values (rewritten by the owning thread at every minute start)
     H_aa, H_cc, H_bD, H_dD,
-    H_COUNT
+    // refined reciprocals of constant divisors (sgm::rcp_nr): x / BW and x / Vi cost 3 instructions
+    H_rBW, H_rVi,
+    // per-thread scratch vectors of the integrator: k1 of the current step (needed again only after a
+    // rejected step and by HINIT) and the two longest-lived stage accumulators (see dopri5_minute)
+    H_K1, H_P7 = H_K1 + 13, H_PE = H_P7 + 13,
+    H_COUNT = H_PE + 13
 };
 
 // Order of the parameter row handed over the C-ABI (include/simglucose_b200.h, sg_param).
@@ -72,6 +77,7 @@ __device__ __forceinline__ void stage_params(const Column<BLOCK> &c, Load p)
     c.set(H_ki, p(P_ki)); c.set(H_m13, m1 + p(P_m30)); c.set(H_m2, m2); c.set(H_kad, ka1 + kd);
     c.set(H_kd, kd); c.set(H_ksc, p(P_ksc)); c.set(H_Vg, p(P_Vg));
     c.set(H_aa, 0.0); c.set(H_cc, 0.0); c.set(H_bD, 0.0); c.set(H_dD, 0.0);
+    c.set(H_rBW, sgm::rcp_nr(p(P_BW))); c.set(H_rVi, sgm::rcp_nr(p(P_Vi)));
 }
 
 // Inputs of the ODE that are constant over one simulated minute (t1dpatient.py:110:
@@ -126,7 +132,7 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     dx[1] = kmax * x[0] - x[1] * kgut;                                      // :145
     const double kabs = c(H_kabs);
     dx[2] = kgut * x[1] - kabs * x[2];                                      // :148
-    const double Rat = sgm::div_nr(c(H_fk) * x[2], c(H_BW));                            // :151
+    const double Rat = sgm::div_r(c(H_fk) * x[2], c(H_BW), c(H_rBW));                            // :151
     const double EGPt = c(H_kp1) - c(H_kp2) * x[3] - c(H_kp3) * x[8];       // :153
     const double ke2 = c(H_ke2);
     const double Et = (x[3] > ke2) ? c(H_ke1) * (x[3] - ke2) : 0.0;         // :158-161
@@ -138,7 +144,7 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     dx[4] = mask_nonneg(x[4], -Uidt + k1 * x[3] - k2 * x[4]);               // :172-173
     const double ka2 = c(H_ka2), m2 = c(H_m2);
     dx[5] = mask_nonneg(x[5], -c(H_m24) * x[5] + c(H_m1) * x[9] + c(H_ka1) * x[10] + ka2 * x[11]);
-    const double It = sgm::div_nr(x[5], c(H_Vi));                                       // :178
+    const double It = sgm::div_r(x[5], c(H_Vi), c(H_rVi));                                     // :178
     const double p2u = c(H_p2u), ki = c(H_ki);
     dx[6] = -p2u * x[6] + p2u * (It - c(H_Ib));                             // :182
     dx[7] = -ki * (x[7] - It);                                              // :185
@@ -252,113 +258,196 @@ struct StepCount { int nstep, nrej; };
 // size is carried over, then the adaptive step loop.  Returns idid (1 ok, -2 nmax, -3 step too small).
 // h_carry: WORK(7) of the Fortran (kept across calls by scipy 1.6.3, zero in scipy >= 1.7).
 //
-// Straight-line form: every stage has its own inlined copy of the RHS, so the stage vectors never move
-// between registers and ptxas can overlap the tail of one stage with the linear combinations of the next.
-// The RHS copies are small (custom exp/division, sg_math.cuh); the step body is one basic block apart
-// from the uniform `fed` test.
+// Shape of the code (sized by profiles/r01_ubench_fp64_icache.log: DFMA latency 8 cycles, one FP64 warp
+// instruction per 2 cycles per sub-partition, instruction fetch collapses once the loop outgrows 32 KB):
+//   * a phase machine around ONE inlined copy of the RHS -- every pass evaluates kt = f(yt), then the arm of
+//     the current phase consumes kt.  All lanes of a warp walk the phases together (uniform switch).
+//   * the stages are never stored.  Hairer's stage sums are evaluated left to right, so each later stage's
+//     sum can be advanced as soon as a k arrives:  P_s += a_sj * k_j  for every s > j.  That is the same
+//     sequence of roundings as  a_s1*k1 + a_s2*k2 + ...  and leaves no k -> register copies.  P3..P6 live in
+//     registers; the two longest-lived sums (stage 7 and the error estimator) live in the thread's
+//     shared-memory column together with k1, which is needed again only by HINIT and after a rejection.
 template <int BLOCK>
 __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minute &m, double (&y)[NX],
-                                             double t0, bool carry_h, double &h_carry, StepCount &cnt)
+                                             double t0, bool carry_h, double &h_carry, StepCount &cnt,
+                                             unsigned lanes)
 {
     const double beta = 0.04, safe = 0.9;
     const double expo1 = 0.2 - beta * 0.75;
     const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
+    enum { PH_K1 = 0, PH_HINIT, PH_S2, PH_S3, PH_S4, PH_S5, PH_S6, PH_S7 };
     double x = t0;
     const double xend = t0 + 1.0;
     const double hmax = fabs(xend - x);
     double facold = 1.0e-4;
     bool last = false, reject = false;
-    int nstep = 0, naccpt = 0, idid = 0;
-    double k1[NX], k2[NX], k3[NX], k4[NX], k5[NX], k6[NX], yt[NX];
+    int nstep = 0, naccpt = 0, idid = 0, phase = PH_K1;
+    double yt[NX], kt[NX], P3[NX], P4[NX], P5[NX], P6[NX];
+    double h = 0.0, dnf = 0.0;
 
-    rhs(c, m, y, k1);
-    double h = carry_h ? h_carry : 0.0;
-    if (h == 0.0) {                                          // HINIT
-        double dnf = 0.0, dny = 0.0;
 #pragma unroll
-        for (int i = 0; i < NX; i++) {
-            const double sk = ATOL + RTOL * fabs(y[i]);
-            const double a = sgm::div_nr(k1[i], sk), b = sgm::div_nr(y[i], sk);
-            dnf = dnf + a * a;
-            dny = dny + b * b;
-        }
-        h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
-        h = fmin(h, hmax);
-#pragma unroll
-        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * k1[i];
-        rhs(c, m, yt, k2);
-        double der2 = 0.0;
-#pragma unroll
-        for (int i = 0; i < NX; i++) {
-            const double sk = ATOL + RTOL * fabs(y[i]);
-            const double a = sgm::div_nr(k2[i] - k1[i], sk);
-            der2 = der2 + a * a;
-        }
-        der2 = sqrt(der2) / h;
-        const double der12 = fmax(fabs(der2), sqrt(dnf));
-        const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
-        h = fmin(fmin(100.0 * fabs(h), h1), hmax);
-    }
+    for (int i = 0; i < NX; i++) yt[i] = y[i];
 
+    // The loop condition is a warp vote: lanes whose minute is complete wait here instead of running ahead
+    // into the next minute on their own (without it ptxas leaves the warp split for the rest of the episode:
+    // 12.8 of 32 lanes active per issued instruction, profiles/r01_i1_*).
 #pragma unroll 1
-    for (;;) {
-        if (nstep > NMAX) { idid = -2; break; }
-        if (0.1 * fabs(h) <= fabs(x) * UROUND) { idid = -3; break; }
-        if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
-        nstep++;
-        {
-            const double ha = h * A21;
+    while (__any_sync(lanes, idid == 0)) {
+        if (idid != 0) continue;
+        rhs(c, m, yt, kt);
+
+        bool begin_step = false;
+        switch (phase) {
+        case PH_K1: {                                        // kt = k1 = f(x, y)
+            h = carry_h ? h_carry : 0.0;
+            if (h == 0.0) {                                  // HINIT, first half
+                double dny = 0.0;
+                dnf = 0.0;
 #pragma unroll
-            for (int i = 0; i < NX; i++) yt[i] = y[i] + ha * k1[i];
+                for (int i = 0; i < NX; i++) { c.set(H_K1 + i, kt[i]); c.set(H_PE + i, y[i]); }
+#pragma unroll 1
+                for (int i = 0; i < NX; i++) {               // rolled: once per minute, keep it out of the I-cache
+                    const double yi = c(H_PE + i);
+                    const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
+                    const double sk = ATOL + RTOL * fabs(yi);
+                    const double a = sgm::div_r(c(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
+                    dnf = dnf + a * a;
+                    dny = dny + b * b;
+                }
+                h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+                h = fmin(h, hmax);
+#pragma unroll
+                for (int i = 0; i < NX; i++) yt[i] = y[i] + h * kt[i];
+                phase = PH_HINIT;
+            } else {
+                begin_step = true;
+            }
+        } break;
+        case PH_HINIT: {                                     // kt = f(x + h, y + h*k1)
+            double der2 = 0.0;
+#pragma unroll
+            for (int i = 0; i < NX; i++) c.set(H_P7 + i, kt[i]);
+#pragma unroll 1
+            for (int i = 0; i < NX; i++) {
+                const double sk = ATOL + RTOL * fabs(c(H_PE + i));
+                const double a = sgm::div_nr(c(H_P7 + i) - c(H_K1 + i), sk);
+                der2 = der2 + a * a;
+            }
+            der2 = sqrt(der2) / h;
+            const double der12 = fmax(fabs(der2), sqrt(dnf));
+            const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
+            h = fmin(fmin(100.0 * fabs(h), h1), hmax);
+#pragma unroll
+            for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
+            begin_step = true;
+        } break;
+        case PH_S2:                                          // kt = k2
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                yt[i] = y[i] + h * (P3[i] + A32 * kt[i]);
+                P4[i] = P4[i] + A42 * kt[i];
+                P5[i] = P5[i] + A52 * kt[i];
+                P6[i] = P6[i] + A62 * kt[i];
+            }
+            phase = PH_S3;
+            break;
+        case PH_S3:                                          // kt = k3
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                yt[i] = y[i] + h * (P4[i] + A43 * kt[i]);
+                P5[i] = P5[i] + A53 * kt[i];
+                P6[i] = P6[i] + A63 * kt[i];
+                c.set(H_P7 + i, c(H_P7 + i) + A73 * kt[i]);
+                c.set(H_PE + i, c(H_PE + i) + E3 * kt[i]);
+            }
+            phase = PH_S4;
+            break;
+        case PH_S4:                                          // kt = k4
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                yt[i] = y[i] + h * (P5[i] + A54 * kt[i]);
+                P6[i] = P6[i] + A64 * kt[i];
+                c.set(H_P7 + i, c(H_P7 + i) + A74 * kt[i]);
+                c.set(H_PE + i, c(H_PE + i) + E4 * kt[i]);
+            }
+            phase = PH_S5;
+            break;
+        case PH_S5:                                          // kt = k5
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                yt[i] = y[i] + h * (P6[i] + A65 * kt[i]);
+                c.set(H_P7 + i, c(H_P7 + i) + A75 * kt[i]);
+                c.set(H_PE + i, c(H_PE + i) + E5 * kt[i]);
+            }
+            phase = PH_S6;
+            break;
+        case PH_S6:                                          // kt = k6; yt becomes the 5th-order solution
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                yt[i] = y[i] + h * (c(H_P7 + i) + A76 * kt[i]);
+                c.set(H_PE + i, c(H_PE + i) + E6 * kt[i]);
+            }
+            phase = PH_S7;
+            break;
+        default: {                                           // kt = k7 = f(x + h, y1): error estimate + control
+            double err = 0.0;
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                const double e = (c(H_PE + i) + E7 * kt[i]) * h;
+                const double sk = ATOL + RTOL * sgm::max_sel(fabs(y[i]), fabs(yt[i]));
+                const double a = sgm::div_nr(e, sk);
+                err = err + a * a;
+            }
+            err = sqrt(sgm::div_nr(err, (double)NX));
+            const double fac11 = sgm::pow_pos(err, expo1);
+            double fac = sgm::div_nr(fac11, sgm::pow_pos(facold, beta));
+            fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
+            double hnew = sgm::div_nr(h, fac);
+            if (err <= 1.0) {
+                facold = sgm::max_sel(err, 1.0e-4);
+                naccpt++;
+#pragma unroll
+                for (int i = 0; i < NX; i++) y[i] = yt[i];   // kt is k1 of the next step (FSAL)
+                x = x + h;
+                if (last) {
+                    idid = 1;
+                } else {
+                    if (fabs(hnew) > hmax) hnew = hmax;
+                    if (reject) hnew = sgm::min_sel(fabs(hnew), fabs(h));
+                    reject = false;
+                    begin_step = true;
+                }
+            } else {
+                hnew = sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
+                reject = true;
+                if (naccpt >= 1) cnt.nrej++;
+                last = false;
+#pragma unroll
+                for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
+                begin_step = true;
+            }
+            h = hnew;
+        } break;
         }
-        rhs(c, m, yt, k2);
+        if (begin_step) {                                    // kt = k1 of the step that starts here
+            if (nstep > NMAX) idid = -2;
+            else if (0.1 * fabs(h) <= fabs(x) * UROUND) idid = -3;
+            else {
+                if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
+                nstep++;
+                const double ha = h * A21;
 #pragma unroll
-        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A31 * k1[i] + A32 * k2[i]);
-        rhs(c, m, yt, k3);
-#pragma unroll
-        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A41 * k1[i] + A42 * k2[i] + A43 * k3[i]);
-        rhs(c, m, yt, k4);
-#pragma unroll
-        for (int i = 0; i < NX; i++) yt[i] = y[i] + h * (A51 * k1[i] + A52 * k2[i] + A53 * k3[i] + A54 * k4[i]);
-        rhs(c, m, yt, k5);
-#pragma unroll
-        for (int i = 0; i < NX; i++)
-            yt[i] = y[i] + h * (A61 * k1[i] + A62 * k2[i] + A63 * k3[i] + A64 * k4[i] + A65 * k5[i]);
-        rhs(c, m, yt, k6);
-#pragma unroll
-        for (int i = 0; i < NX; i++)
-            yt[i] = y[i] + h * (A71 * k1[i] + A73 * k3[i] + A74 * k4[i] + A75 * k5[i] + A76 * k6[i]);
-        rhs(c, m, yt, k2);                                   // k7 = f(x + h, y1), kept in k2 (FSAL)
-        double err = 0.0;
-#pragma unroll
-        for (int i = 0; i < NX; i++) {
-            const double e = (E1 * k1[i] + E3 * k3[i] + E4 * k4[i] + E5 * k5[i] + E6 * k6[i] + E7 * k2[i]) * h;
-            const double sk = ATOL + RTOL * fmax(fabs(y[i]), fabs(yt[i]));
-            const double a = sgm::div_nr(e, sk);
-            err = err + a * a;
+                for (int i = 0; i < NX; i++) {
+                    const double k = kt[i];
+                    c.set(H_K1 + i, k);
+                    yt[i] = y[i] + ha * k;
+                    P3[i] = A31 * k; P4[i] = A41 * k; P5[i] = A51 * k; P6[i] = A61 * k;
+                    c.set(H_P7 + i, A71 * k);
+                    c.set(H_PE + i, E1 * k);
+                }
+                phase = PH_S2;
+            }
         }
-        err = sqrt(err / (double)NX);
-        const double fac11 = sgm::pow_pos(err, expo1);
-        double fac = fac11 / sgm::pow_pos(facold, beta);
-        fac = fmax(facc2, fmin(facc1, fac / safe));
-        double hnew = h / fac;
-        if (err <= 1.0) {
-            facold = fmax(err, 1.0e-4);
-            naccpt++;
-#pragma unroll
-            for (int i = 0; i < NX; i++) { k1[i] = k2[i]; y[i] = yt[i]; }
-            x = x + h;
-            if (last) { h = hnew; idid = 1; break; }
-            if (fabs(hnew) > hmax) hnew = hmax;
-            if (reject) hnew = fmin(fabs(hnew), fabs(h));
-            reject = false;
-        } else {
-            hnew = h / fmin(facc1, fac11 / safe);
-            reject = true;
-            if (naccpt >= 1) cnt.nrej++;
-            last = false;
-        }
-        h = hnew;
     }
     if (carry_h) h_carry = h;
     cnt.nstep += nstep;
