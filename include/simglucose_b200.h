@@ -134,8 +134,9 @@ int sg_set_t0(sg_handle h, int32_t t0);
 /* T1DPatient.step (patient/t1dpatient.py:82-116) for every episode: meal state machine + one minute of
  * dopri5 with an explicit patient Action(CHO = grams announced this minute, insulin U/min).
  * out [SG_NPOUT][E] (may be NULL): x[13], Gsub (observation, t1dpatient.py:210-220), grams eaten this
- * minute, idid of this call, DOPRI5 steps taken. */
-#define SG_NPOUT 17
+ * minute, idid of this call, DOPRI5 steps taken, then the meal machine after the minute: planned_meal,
+ * _last_Qsto, _last_foodtaken, is_eating (t1dpatient.py:88-104, 222-236). */
+#define SG_NPOUT 21
 int sg_patient_step(sg_handle h, const double *cho, const double *insulin, double *out, void *stream);
 
 /* T1DPatient.model (patient/t1dpatient.py:118-208): dxdt [SG_NX][n] for n independent evaluations.
@@ -151,6 +152,16 @@ int sg_pump(const double *amount, double *out, int64_t n, double vmin, double vm
 /* risk_index([BG], 1) (analysis/risk.py:5-17), elementwise: out [3][n] = LBGI, HBGI, RI. */
 int sg_risk_index(const double *bg, double *out, int64_t n, void *stream);
 
+/* risk_index(BG, horizon) (analysis/risk.py:5-17) over a window: bg [n] holds BG[-horizon:]; out [3] = LBGI,
+ * HBGI, RI with LBGI = mean of 10 f^2 over the samples with f < 0 (0 when there are none), HBGI likewise
+ * for f > 0.  One block, fixed-order sums. */
+int sg_risk_window(const double *bg, double *out, int64_t n, void *stream);
+
+/* The sampling branch of CGMSensor.measure (sensor/cgm.py:28-33), elementwise:
+ * out[i] = min(max(bg[i] + noise[i], sensor_min), sensor_max). */
+int sg_cgm_measure(const double *bg, const double *noise, double *out, int64_t n, double sensor_min,
+                   double sensor_max, void *stream);
+
 /* SimObj.simulate (simulation/sim_engine.py:29-39) for every episode, n_steps env-steps fused in
  * one launch with the controller evaluated on device.
  *   ctrl_host [SG_NCTRL]      controller constants used for every episode when ctrl_rows is NULL
@@ -161,7 +172,34 @@ int sg_risk_index(const double *bg, double *out, int64_t n, void *stream);
 int sg_run(sg_handle h, int32_t controller, const double *ctrl_host, const double *ctrl_rows,
            const double *actions, int32_t n_steps, double *trace, int32_t *counters, void *stream);
 
+/* Rows of the resident per-episode state as sg_get_episode_state returns it. */
+typedef enum {
+    SG_D_X = 0,              /* 13 rows: patient state                              t1dpatient.py:238-240 */
+    SG_D_PLANNED = 13,       /* planned_meal                                        t1dpatient.py:225 */
+    SG_D_LAST_CHO,           /* _last_action.CHO                                    t1dpatient.py:106 */
+    SG_D_LAST_QSTO,          /* _last_Qsto                                          t1dpatient.py:90 */
+    SG_D_LAST_FOOD,          /* _last_foodtaken                                     t1dpatient.py:91,99 */
+    SG_D_H_CARRY,            /* dopri5 WORK(7) (SG_FLAG_CARRY_H only) */
+    SG_D_LAST_CGM,           /* CGMSensor._last_CGM                                 cgm.py:33 */
+    SG_D_CGM_PREV,           /* CGM_hist[-1]                                        env.py:96 */
+    SG_D_OBS,                /* last observation.CGM                                env.py:105,142 */
+    SG_D_INFO_MEAL,          /* info['meal'] of the last step                       env.py:112 */
+    SG_D_PID_INTEG,          /* PIDController.integrated_state                      pid_ctrller.py:15 */
+    SG_D_PID_PREV,           /* PIDController.prev_state                            pid_ctrller.py:16 */
+    SG_ND
+} sg_state_d;
+typedef enum {
+    SG_I_EATING = 0,         /* is_eating                                           t1dpatient.py:92,104 */
+    SG_I_MINUTE,             /* patient.t as an integer minute                      t1dpatient.py:73-75 */
+    SG_I_NOISE_POS,          /* noise samples consumed */
+    SG_I_MEAL_POS,           /* next unconsumed meal-table entry */
+    SG_I_STATUS,             /* scipy idid of the first failed minute, else 1 */
+    SG_NI
+} sg_state_i;
+
 /* Resident state readers (T1DPatient.state t1dpatient.py:238-240; env histories). */
+/* The whole resident state: d_out [SG_ND][E] and i_out [SG_NI][E] (either may be NULL). */
+int sg_get_episode_state(sg_handle h, double *d_out, int32_t *i_out, void *stream);
 int sg_get_state(sg_handle h, double *x_out /* [SG_NX][E] */, void *stream);
 int sg_get_stats(sg_handle h, double *stats_out /* [SG_NSTAT][E] */, void *stream);
 /* Per-episode solver status: 1 ok, -2 (more than 500 steps), -3 (step size too small): scipy's idid,

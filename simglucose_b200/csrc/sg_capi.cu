@@ -12,6 +12,8 @@ static_assert(SG_NSTAT == sgk::NSTAT, "stat columns");
 static_assert(SG_NCTRL == sgk::NCTRL, "controller constants");
 static_assert(SG_NPOUT == sgk::NPOUT, "patient step rows");
 static_assert(SG_NPARAM == 32 && SG_NX == 13, "table shapes");
+static_assert(SG_ND == sgk::SD_COUNT && SG_NI == sgk::SI_COUNT, "resident state rows");
+static_assert(SG_D_PID_PREV == sgk::SD_PID_PREV && SG_I_STATUS == sgk::SI_STATUS, "resident state order");
 
 namespace {
 
@@ -288,7 +290,7 @@ int sg_model(sg_handle h, int64_t n, const double *x, const double *cho, const d
 int sg_pump(const double *amount, double *out, int64_t n, double vmin, double vmax, double inc, void *stream)
 {
     if (!amount || !out || n <= 0 || !(inc > 0.0)) return fail(SG_ERR_ARG, "sg_pump: bad arguments");
-    sgk::ElementwiseArgs a{n, amount, out, {vmin, vmax, inc}};
+    sgk::ElementwiseArgs a{n, amount, out, {vmin, vmax, inc}, nullptr};
     cudaError_t ce = sg_strict::launch_pump(a, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_pump: launch", ce);
     return SG_OK;
@@ -297,9 +299,28 @@ int sg_pump(const double *amount, double *out, int64_t n, double vmin, double vm
 int sg_risk_index(const double *bg, double *out, int64_t n, void *stream)
 {
     if (!bg || !out || n <= 0) return fail(SG_ERR_ARG, "sg_risk_index: bad arguments");
-    sgk::ElementwiseArgs a{n, bg, out, {0.0, 0.0, 0.0}};
+    sgk::ElementwiseArgs a{n, bg, out, {0.0, 0.0, 0.0}, nullptr};
     cudaError_t ce = sg_strict::launch_risk(a, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_risk_index: launch", ce);
+    return SG_OK;
+}
+
+int sg_risk_window(const double *bg, double *out, int64_t n, void *stream)
+{
+    if (!bg || !out || n <= 0) return fail(SG_ERR_ARG, "sg_risk_window: bad arguments");
+    sgk::ElementwiseArgs a{n, bg, out, {0.0, 0.0, 0.0}, nullptr};
+    cudaError_t ce = sg_strict::launch_risk_window(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_risk_window: launch", ce);
+    return SG_OK;
+}
+
+int sg_cgm_measure(const double *bg, const double *noise, double *out, int64_t n, double sensor_min,
+                   double sensor_max, void *stream)
+{
+    if (!bg || !noise || !out || n <= 0) return fail(SG_ERR_ARG, "sg_cgm_measure: bad arguments");
+    sgk::ElementwiseArgs a{n, bg, out, {sensor_min, sensor_max, 0.0}, noise};
+    cudaError_t ce = sg_strict::launch_cgm(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_cgm_measure: launch", ce);
     return SG_OK;
 }
 
@@ -325,6 +346,17 @@ static int copy_out(sg_handle h, void *dst, const void *src, size_t elem, int ro
 int sg_get_state(sg_handle h, double *x_out, void *stream)
 {
     return copy_out(h, x_out, h ? h->sd : nullptr, sizeof(double), SG_NX, stream, "sg_get_state");
+}
+
+int sg_get_episode_state(sg_handle h, double *d_out, int32_t *i_out, void *stream)
+{
+    if (!h || (!d_out && !i_out)) return fail(SG_ERR_ARG, "sg_get_episode_state: null argument");
+    if (d_out) {
+        int rc = copy_out(h, d_out, h->sd, sizeof(double), SG_ND, stream, "sg_get_episode_state");
+        if (rc != SG_OK) return rc;
+    }
+    if (i_out) return copy_out(h, i_out, h->si, sizeof(int32_t), SG_NI, stream, "sg_get_episode_state");
+    return SG_OK;
 }
 
 int sg_get_stats(sg_handle h, double *stats_out, void *stream)

@@ -303,6 +303,10 @@ __global__ void __launch_bounds__(BLOCK) patient_step_kernel(const PatientArgs p
         o[(int64_t)14 * a.n] = to_eat;
         o[(int64_t)15 * a.n] = (double)idid;
         o[(int64_t)16 * a.n] = (double)cnt.nstep;
+        o[(int64_t)17 * a.n] = meal.planned;
+        o[(int64_t)18 * a.n] = meal.last_Qsto;
+        o[(int64_t)19 * a.n] = meal.last_food;
+        o[(int64_t)20 * a.n] = (double)meal.eating;
     }
 }
 
@@ -339,6 +343,41 @@ __global__ void __launch_bounds__(256) risk_kernel(const ElementwiseArgs a)
     double l, h, r;
     risk_index(a.in[i], l, h, r);
     a.out[i] = l; a.out[a.n + i] = h; a.out[2 * a.n + i] = r;
+}
+
+// The sampling branch of CGMSensor.measure (cgm.py:28-33), elementwise; p = sensor min, max.
+__global__ void __launch_bounds__(256) cgm_kernel(const ElementwiseArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= a.n) return;
+    double cgm = a.in[i] + a.in2[i];
+    cgm = (a.p[0] > cgm) ? a.p[0] : cgm;
+    cgm = (a.p[1] < cgm) ? a.p[1] : cgm;
+    a.out[i] = cgm;
+}
+
+// risk_index(BG, horizon) over a window (risk.py:5-17): means of 10 f^2 over the negative / positive f.
+// One block; every thread accumulates a strided slice in index order, thread 0 adds the slices in order.
+__global__ void __launch_bounds__(256) risk_window_kernel(const ElementwiseArgs a)
+{
+    __shared__ double part[256][4];
+    double sl = 0.0, sh = 0.0, nl = 0.0, nh = 0.0;
+    for (int64_t i = threadIdx.x; i < a.n; i += 256) {
+        const double f = 1.509 * (pow(log(a.in[i]), 1.084) - 5.381);
+        if (f < 0.0) { sl += 10.0 * (f * f); nl += 1.0; }
+        if (f > 0.0) { sh += 10.0 * (f * f); nh += 1.0; }
+    }
+    part[threadIdx.x][0] = sl; part[threadIdx.x][1] = sh; part[threadIdx.x][2] = nl; part[threadIdx.x][3] = nh;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        sl = sh = nl = nh = 0.0;
+        for (int t = 0; t < 256; t++) { sl += part[t][0]; sh += part[t][1]; nl += part[t][2]; nh += part[t][3]; }
+        double lbgi = nl > 0.0 ? sl / nl : 0.0;      // nan_to_num(mean of an empty selection) == 0
+        double hbgi = nh > 0.0 ? sh / nh : 0.0;
+        if (isinf(lbgi)) lbgi = DBL_MAX;
+        if (isinf(hbgi)) hbgi = DBL_MAX;
+        a.out[0] = lbgi; a.out[1] = hbgi; a.out[2] = lbgi + hbgi;
+    }
 }
 
 // Accuracy probe of the helpers in sg_math.cuh against CUDA's libm (tests/test_gpu_math.py).
@@ -476,6 +515,18 @@ cudaError_t launch_pump(const ElementwiseArgs &a, cudaStream_t s)
 cudaError_t launch_risk(const ElementwiseArgs &a, cudaStream_t s)
 {
     risk_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cgm(const ElementwiseArgs &a, cudaStream_t s)
+{
+    cgm_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_risk_window(const ElementwiseArgs &a, cudaStream_t s)
+{
+    risk_window_kernel<<<1, 256, 0, s>>>(a);
     return cudaGetLastError();
 }
 

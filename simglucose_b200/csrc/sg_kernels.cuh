@@ -79,7 +79,7 @@ struct EpisodeArgs {
 };
 
 // T1DPatient.step for every episode: one minute with an explicit Action(CHO announced, insulin).
-constexpr int NPOUT = 17;      // out rows: x[13], Gsub, to_eat, idid, dopri5 steps
+constexpr int NPOUT = 21;      // out rows: x[13], Gsub, to_eat, idid, dopri5 steps, planned, last_Qsto, last_food, eating
 struct PatientArgs {
     EpisodeArgs e;
     const double *cho;         // [n] grams announced this minute
@@ -103,6 +103,7 @@ struct ElementwiseArgs {
     const double *in;
     double *out;
     double p[3];
+    const double *in2;         // second operand (cgm_kernel: noise)
 };
 
 struct ReduceArgs {
@@ -122,6 +123,8 @@ struct ReduceArgs {
     cudaError_t launch_model(const sgk::ModelArgs &a, cudaStream_t s);        \
     cudaError_t launch_pump(const sgk::ElementwiseArgs &a, cudaStream_t s);   \
     cudaError_t launch_risk(const sgk::ElementwiseArgs &a, cudaStream_t s);   \
+    cudaError_t launch_cgm(const sgk::ElementwiseArgs &a, cudaStream_t s);    \
+    cudaError_t launch_risk_window(const sgk::ElementwiseArgs &a, cudaStream_t s); \
     cudaError_t launch_math_probe(int kind, const double *a, const double *b, double *out, int64_t n, cudaStream_t s); \
     int reduce_blocks(int64_t n);                                             \
     }
