@@ -200,6 +200,10 @@ typedef enum {
 /* Resident state readers (T1DPatient.state t1dpatient.py:238-240; env histories). */
 /* The whole resident state: d_out [SG_ND][E] and i_out [SG_NI][E] (either may be NULL). */
 int sg_get_episode_state(sg_handle h, double *d_out, int32_t *i_out, void *stream);
+/* The inverse: overwrite the resident state of the n_episodes of the last sg_reset (checkpoint / resume, and
+ * handing episodes simulated in one batch back to per-patient handles).  Either pointer may be NULL.
+ * steps_done = env-steps these episodes have already taken (what the noise-stream length check counts). */
+int sg_set_episode_state(sg_handle h, const double *d_in, const int32_t *i_in, int64_t steps_done, void *stream);
 int sg_get_state(sg_handle h, double *x_out /* [SG_NX][E] */, void *stream);
 int sg_get_stats(sg_handle h, double *stats_out /* [SG_NSTAT][E] */, void *stream);
 /* Per-episode solver status: 1 ok, -2 (more than 500 steps), -3 (step size too small): scipy's idid,

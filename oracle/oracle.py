@@ -59,6 +59,8 @@ def lib():
                                     dp, dp, dp, C.c_int]
         L.sgo_run_batch.restype = C.c_int
         L.sgo_max_threads.restype = C.c_int
+        L.sgo_dopri5_minute.argtypes = [dp, dp, dp, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, dp, ip]
+        L.sgo_dopri5_minute.restype = C.c_int
         _lib = L
     return _lib
 

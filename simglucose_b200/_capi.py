@@ -32,7 +32,7 @@ SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_har
            'sg_reset', 'sg_step', 'sg_run', 'sg_get_state', 'sg_get_stats', 'sg_get_status',
            'sg_reduce_stats', 'sg_num_episodes', 'sg_launch_count',
            'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_patient_step', 'sg_model', 'sg_pump',
-           'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_math_probe',
+           'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
            'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma']
 
 
@@ -77,6 +77,7 @@ def load():
     L.sg_risk_window.argtypes = [dp, dp, C.c_int64, vp]
     L.sg_cgm_measure.argtypes = [dp, dp, dp, C.c_int64, C.c_double, C.c_double, vp]
     L.sg_get_episode_state.argtypes = [vp, dp, ip, vp]
+    L.sg_set_episode_state.argtypes = [vp, dp, ip, C.c_int64, vp]
     L.sg_math_probe.argtypes = [C.c_int32, dp, dp, dp, C.c_int64, vp]
     L.sg_get_state.argtypes = [vp, dp, vp]
     L.sg_get_stats.argtypes = [vp, dp, vp]

@@ -359,6 +359,23 @@ int sg_get_episode_state(sg_handle h, double *d_out, int32_t *i_out, void *strea
     return SG_OK;
 }
 
+int sg_set_episode_state(sg_handle h, const double *d_in, const int32_t *i_in, int64_t steps_done, void *stream)
+{
+    if (!h || (!d_in && !i_in) || steps_done < 0) return fail(SG_ERR_ARG, "sg_set_episode_state: bad arguments");
+    if (!h->is_reset) return fail(SG_ERR_STATE, "sg_set_episode_state: call sg_reset first");
+    DeviceGuard g(h->device);
+    cudaError_t ce = cudaSuccess;
+    if (d_in)
+        ce = cudaMemcpy2DAsync(h->sd, sizeof(double) * h->cap, d_in, sizeof(double) * h->n, sizeof(double) * h->n,
+                               SG_ND, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+    if (ce == cudaSuccess && i_in)
+        ce = cudaMemcpy2DAsync(h->si, sizeof(int32_t) * h->cap, i_in, sizeof(int32_t) * h->n, sizeof(int32_t) * h->n,
+                               SG_NI, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_set_episode_state: copy", ce);
+    h->steps_done = steps_done;
+    return SG_OK;
+}
+
 int sg_get_stats(sg_handle h, double *stats_out, void *stream)
 {
     return copy_out(h, stats_out, h ? h->stats : nullptr, sizeof(double), SG_NSTAT, stream, "sg_get_stats");

@@ -32,7 +32,9 @@ __device__ __forceinline__ ParamLoad param_source(const EpisodeArgs &a, int64_t 
 // CGMSensor.measure at a sampling minute, cgm.py:28-33.
 __device__ __forceinline__ double cgm_sample(const EpisodeArgs &a, int64_t e, double bg, int &noise_pos)
 {
-    double cgm = bg + a.noise[(int64_t)noise_pos * a.n + e];
+    // the C-ABI checks the stream length against the steps taken; the guard covers episode states that were
+    // uploaded with a position of their own (sg_set_episode_state)
+    double cgm = bg + (noise_pos < a.n_noise ? a.noise[(int64_t)noise_pos * a.n + e] : 0.0);
     noise_pos++;
     cgm = (a.hw.smin > cgm) ? a.hw.smin : cgm;   // max(CGM, min)
     cgm = (a.hw.smax < cgm) ? a.hw.smax : cgm;   // min(CGM, max)

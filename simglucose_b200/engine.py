@@ -119,6 +119,44 @@ class BatchEngine:
         self.steps_done += 1
         return out
 
+    def step_meals(self, basal, bolus, meals, out=None):
+        """T1DSimEnv.step with this step's announced meals supplied by the caller: meals [sample_time, E] =
+        scenario.get_action(time).meal for each minute of the step (env.py:50) -- the seam for arbitrary
+        Scenario subclasses evaluated on the host."""
+        b = self._dev(basal, torch.float64, 1)
+        o = self._dev(bolus, torch.float64, 1)
+        m = self._dev(meals, torch.float64, self.sample_time)
+        if out is None:
+            out = self.empty(_capi.NTRACE)
+        _capi.check(self.lib.sg_step_meals(self._h, _ptr(b), _ptr(o), _ptr(m), _ptr(out), _stream_ptr()))
+        self.steps_done += 1
+        return out
+
+    def patient_step(self, cho, insulin, out=None):
+        """T1DPatient.step for every episode: one minute with Action(CHO = grams announced, insulin U/min).
+        Returns [NPOUT, E]: x[13], Gsub, to_eat, idid, dopri5 steps, planned_meal, _last_Qsto,
+        _last_foodtaken, is_eating."""
+        c = self._dev(cho, torch.float64, 1)
+        i = self._dev(insulin, torch.float64, 1)
+        if out is None:
+            out = self.empty(_capi.NPOUT)
+        _capi.check(self.lib.sg_patient_step(self._h, _ptr(c), _ptr(i), _ptr(out), _stream_ptr()))
+        return out
+
+    def set_t0(self, t0):
+        """patient.t at the next reset (T1DPatient(t0=...), t1dpatient.py:27,277)."""
+        _capi.check(self.lib.sg_set_t0(self._h, int(t0)))
+
+    def rebind_streams(self, noise, meal_minute=None, meal_grams=None):
+        """Swap in longer noise / meal buffers without resetting the episodes."""
+        nz = self._dev(noise, torch.float64)
+        mm = self._dev(meal_minute, torch.int32)
+        mg = self._dev(meal_grams, torch.float64)
+        max_meals = 0 if mm is None else mm.shape[0]
+        _capi.check(self.lib.sg_rebind_streams(self._h, _ptr(mm), _ptr(mg), max_meals, _ptr(nz), nz.shape[0]))
+        torch.cuda.current_stream().synchronize()       # kernels in flight may still read the old buffers
+        self._keep.update(nz=nz, mm=mm, mg=mg)
+
     def run(self, n_steps, controller='bb', ctrl=None, ctrl_rows=None, actions=None, trace=True, counters=False):
         """SimObj.simulate for every episode, n_steps env-steps in one launch.
 
@@ -148,6 +186,44 @@ class BatchEngine:
     def state(self):
         out = self.empty(_capi.NX)
         _capi.check(self.lib.sg_get_state(self._h, _ptr(out), _stream_ptr()))
+        return out
+
+    def episode_state(self):
+        """The whole resident state: (d [ND, E] float64, i [NI, E] int32); rows: include/simglucose_b200.h
+        sg_state_d / sg_state_i."""
+        d = self.empty(_capi.ND)
+        i = self.empty(_capi.NI, dtype=torch.int32)
+        _capi.check(self.lib.sg_get_episode_state(self._h, _ptr(d), _ptr(i), _stream_ptr()))
+        return d, i
+
+    def set_episode_state(self, d=None, i=None, steps_done=None):
+        """Overwrite the resident state; steps_done = env-steps those episodes have already taken (keeps the
+        noise-stream length checks valid)."""
+        dd = self._dev(d, torch.float64, _capi.ND)
+        ii = self._dev(i, torch.int32, _capi.NI)
+        sd = self.steps_done if steps_done is None else int(steps_done)
+        _capi.check(self.lib.sg_set_episode_state(self._h, _ptr(dd), _ptr(ii), sd, _stream_ptr()))
+        self.steps_done = sd
+        torch.cuda.current_stream().synchronize()
+
+    def model(self, x, cho, insulin, last_qsto, last_food, patient_row=None, params=None):
+        """T1DPatient.model for n independent evaluations: x [13, n]; cho, insulin, last_qsto, last_food [n];
+        params [32, n] or patient_row [n] into the loaded table.  Returns dxdt [13, n]."""
+        def dev(a, dtype=torch.float64):
+            t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+            return t.to(device=self.device, dtype=dtype).contiguous()
+        xt = dev(x)
+        n = xt.shape[-1]
+        assert xt.shape == (_capi.NX, n)
+        args = [dev(np.broadcast_to(np.asarray(a, dtype=np.float64), (n,)).copy() if not isinstance(a, torch.Tensor) else a)
+                for a in (cho, insulin, last_qsto, last_food)]
+        pr = dev(patient_row, torch.int32) if patient_row is not None else None
+        pt = dev(params) if params is not None else None
+        if pt is not None:
+            assert pt.shape == (_capi.NPARAM, n)
+        out = torch.empty(_capi.NX, n, dtype=torch.float64, device=self.device)
+        _capi.check(self.lib.sg_model(self._h, n, _ptr(xt), _ptr(args[0]), _ptr(args[1]), _ptr(args[2]), _ptr(args[3]),
+                                      _ptr(pr), _ptr(pt), _ptr(out), _stream_ptr()))
         return out
 
     def stats(self):

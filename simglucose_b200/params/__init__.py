@@ -73,7 +73,9 @@ def sensor_params(name='Dexcom'):
     cols, rows = _rows('sensor_params')
     for r in rows:
         if r[0] == name:
-            return dict(zip(cols, r))
+            d = dict(zip(cols, r))
+            d['sample_time'] = int(d['sample_time'])      # an integer column in sensor_params.csv
+            return d
     raise KeyError(name)
 
 
@@ -91,3 +93,11 @@ def sensor_names():
 
 def pump_names():
     return [r[0] for r in _rows('pump_params')[1]]
+
+
+def patient_series(row):
+    """The pandas Series the reference hands to T1DPatient (one row of vpatient_params.csv, all 62
+    columns in file order, so that params.iloc[2:15] is x0 and params.BW etc. work)."""
+    import pandas as pd
+    cols, rows = _rows('vpatient_params')
+    return pd.Series(rows[row], index=cols, name=row)
