@@ -144,38 +144,59 @@ def cpu_sample(args, noise_h, mm_h, mg_h, rows_h, n_steps, threads, target_s):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU implementation of the path.  The reference is pure Python and
-    cannot travel to the GPU box, so this is the C oracle port on all host threads (cpu_baseline.kind
-    'port'), each step a bounded sample of the same workload generated on the host with numpy."""
+    """--impl reference: the reference's CPU implementation of the path on the box's host cores.  The
+    reference is pure Python and cannot travel to the GPU box, so this is the C oracle port
+    (oracle/sg_oracle.c, cpu_baseline.kind 'port') on all host threads.  Each step is a bounded sample of
+    the bench workload (same patients, controller, scenario / noise distributions, generated on the host
+    with the reference-compatible MT19937 generators), sized by a calibration pass to a few seconds."""
     if rank != 0:
         return
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import oracle as O
-    from simglucose_b200 import streams as S
+    from simglucose_b200 import streams as S, params as P
     threads = O.max_threads()
     n_steps = args.days * 480
-    groups = max(1, (threads * 2 + 29) // 30)
-    E = groups * 30
-    rows = (np.arange(E) % 30).astype(np.int32)
-    noise = np.repeat(np.stack([S.cgm_noise_stream('Dexcom', g, n_steps + 2) for g in range(groups)], 1), 30, axis=1)
-    tabs = [S.random_scenario_table(g, 0, n_steps * 3) for g in range(groups)]
-    mm, mg = S.pad_tables([tabs[e // 30] for e in range(E)])
-    times = []
-    res = None
-    for it in range(args.warmup + args.steps):
+    n_min = n_steps * 3
+    tbl, x0 = P.cohort_table()
+
+    def make(groups):
+        E = groups * 30
+        rows = (np.arange(E) % 30).astype(np.int32)
+        noise = np.repeat(np.stack([S.cgm_noise_stream('Dexcom', g, n_steps + 2) for g in range(groups)], 0), 30, axis=0)
+        tabs = [S.random_scenario_table(g, 0, n_min) for g in range(groups)]
+        mm, mg = S.pad_tables([tabs[e // 30] for e in range(E)])
+        ctrl = controller_rows(rows).T.copy()[:, [0, 1, 2, 3, 3, 3]]
+        return dict(E=E, P=tbl[rows], x0=x0[rows], mm=mm.T.copy(), mg=mg.T.copy(), noise=noise, ctrl=ctrl)
+
+    def run(w):
         t0 = time.perf_counter()
-        res = cpu_sample(args, noise, mm, mg, rows, n_steps, threads, target_s=0.0)
+        st, failed = O.run_batch(w['P'], w['x0'], n_steps, w['mm'], w['mg'], w['noise'], controller='bb',
+                                 ctrl_rows=w['ctrl'], carry_h=int(args.carry_h), n_threads=threads)
+        return time.perf_counter() - t0, st, failed
+
+    cal = make(max(1, (4 * threads + 29) // 30))
+    dt, _, _ = run(cal)                                               # calibration
+    rate = cal['E'] * n_min / dt
+    groups = int(max(1, min(4096, round(rate * 4.0 / n_min / 30))))   # ~4 s of CPU work per step
+    w = make(groups)
+    times, st, failed = [], None, 0
+    for it in range(args.warmup + args.steps):
+        dt, st, failed = run(w)
         if it >= args.warmup:
-            times.append(res['value'])
-    v = float(np.mean(times))
-    res['value'] = v
+            times.append(dt)
+    sec = float(np.mean(times))
+    v = w['E'] * n_min / sec
+    sample = ('%d episodes (30 patients x %d seed groups) x %d min per step, %.2f s per step, oracle/sg_oracle.c '
+              'over %d pthreads' % (w['E'], groups, n_min, sec, threads))
+    cpu = {'value': v, 'unit': METRIC, 'cores': threads, 'kind': 'port', 'sample': sample, 'failed': int(failed),
+           'mean_dopri_steps_per_min': float(st[:, 14].sum() / (w['E'] * n_min))}
     line = {'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': METRIC, 'n_gpus': args.gpus,
-            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * E * n_steps * 3 / v,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * sec,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': 'configs[1] cohort: 30 patients x %d seed groups x %d-day RandomScenario, '
-                                   'BBController (bounded CPU sample)' % (groups, args.days),
-                       'episodes': E, 'minutes_per_episode': n_steps * 3},
-            'cpu_baseline': res,
+            'config': {'workload': 'configs[1] cohort: 30 virtual patients x seed groups x %d-day RandomScenario, '
+                                   'BBController, Dexcom, Insulet (bounded CPU sample: %d seed groups)' % (args.days, groups),
+                       'episodes': w['E'], 'minutes_per_episode': n_min, 'carry_h': bool(args.carry_h)},
+            'cpu_baseline': cpu,
             'e2e': {'value': v, 'unit': METRIC, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
     print(json.dumps(line))
 
