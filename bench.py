@@ -175,6 +175,7 @@ def run_reference(args, rank, world):
         return time.perf_counter() - t0, st, failed
 
     cal = make(max(1, (4 * threads + 29) // 30))
+    run(cal)                                                          # library load, thread start-up
     dt, _, _ = run(cal)                                               # calibration
     rate = cal['E'] * n_min / dt
     groups = int(max(1, min(4096, round(rate * 4.0 / n_min / 30))))   # ~4 s of CPU work per step
