@@ -58,6 +58,21 @@ __device__ __forceinline__ void stats_add_row(double (&s)[NSTAT], double bg, dou
     if (done && s[13] < 0.0) s[13] = row;
 }
 
+// The same on the resident statistics (global memory, one coalesced read-modify-write per env-step): the 16
+// accumulators would otherwise hold 32 registers across the integrator, which needs them for scheduling.
+__device__ __forceinline__ void stats_add_row_resident(double *st, int64_t cap, double bg, double lbgi, double hbgi,
+                                                       double ri, double reward, bool done, int nstep, int nrej)
+{
+    double s[NSTAT];
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) s[i] = st[(int64_t)i * cap];
+    stats_add_row(s, bg, lbgi, hbgi, ri, reward, done);
+    s[14] += (double)nstep;
+    s[15] += (double)nrej;
+#pragma unroll
+    for (int i = 0; i < NSTAT; i++) st[(int64_t)i * cap] = s[i];
+}
+
 __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
 {
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
@@ -126,7 +141,6 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     const Column<BLOCK> c{smem + threadIdx.x};
     const ParamLoad p = param_source(a, e);
     stage_params(c, p);
-    const double u2ss = p(P_u2ss);
 
     double *sd = a.sd + e;
     int32_t *si = a.si + e;
@@ -141,22 +155,13 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     meal.eating = si[(int64_t)SI_EATING * a.cap];
     double h_carry = sd[(int64_t)SD_H_CARRY * a.cap];
     double last_cgm = sd[(int64_t)SD_LAST_CGM * a.cap];
-    double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
-    double obs = sd[(int64_t)SD_OBS * a.cap];
-    double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
-    double pid_integ = sd[(int64_t)SD_PID_INTEG * a.cap];
-    double pid_prev = sd[(int64_t)SD_PID_PREV * a.cap];
+    // cgm_prev, obs, info_meal and the PID state are only touched at env-step boundaries: they stay in the
+    // resident state (global memory, L2 hits) instead of holding registers across the integrator
     int minute = si[(int64_t)SI_MINUTE * a.cap];
     int noise_pos = si[(int64_t)SI_NOISE_POS * a.cap];
     int meal_pos = si[(int64_t)SI_MEAL_POS * a.cap];
     int status = si[(int64_t)SI_STATUS * a.cap];
-    double s[NSTAT];
-#pragma unroll
-    for (int i = 0; i < NSTAT; i++) s[i] = a.stats[(int64_t)i * a.cap + e];
-
-    double ctrl[NCTRL];
-#pragma unroll
-    for (int i = 0; i < NCTRL; i++) ctrl[i] = a.ctrl_rows ? a.ctrl_rows[(int64_t)i * a.n + e] : a.ctrl[i];
+    int step_nstep = 0, step_nrej = 0;             // DOPRI5 steps / rejects of the current env-step
 
     const int st_i = a.hw.st;
     const double st = (double)st_i;
@@ -165,8 +170,14 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     for (int k = 0; k < a.n_steps; k++) {
         // ---- controller.policy(observation, reward, done, **info) ----
         double a_basal, a_bolus;
+        double ctrl[NCTRL];                            // re-read per env-step (L2 resident): not live across the integrator
+#pragma unroll
+        for (int i = 0; i < NCTRL; i++) ctrl[i] = a.ctrl_rows ? __ldg(a.ctrl_rows + (int64_t)i * a.n + e) : a.ctrl[i];
+        const double obs = sd[(int64_t)SD_OBS * a.cap];
+        const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
         if (a.controller == 1) {                       // BBController._bb_policy
-            a_basal = u2ss * c(H_BW) / 6000.0;
+            const double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
+            a_basal = __ldg(&p.base[P_u2ss * p.stride]) * c(H_BW) / 6000.0;
             if (info_meal > 0.0) {
                 const double corr = (obs > 150.0 ? 1.0 : 0.0) * (obs - ctrl[0]) / ctrl[2];
                 a_bolus = (info_meal * st) / ctrl[1] + corr;
@@ -175,9 +186,11 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
             }
             a_bolus = a_bolus / st;
         } else if (a.controller == 2) {                // PIDController.policy
+            const double pid_integ = sd[(int64_t)SD_PID_INTEG * a.cap];
+            const double pid_prev = sd[(int64_t)SD_PID_PREV * a.cap];
             a_basal = ctrl[0] * (obs - ctrl[3]) + ctrl[1] * pid_integ + ctrl[2] * (obs - pid_prev) / st;
-            pid_prev = obs;
-            pid_integ += (obs - ctrl[3]) * st;
+            sd[(int64_t)SD_PID_PREV * a.cap] = obs;
+            sd[(int64_t)SD_PID_INTEG * a.cap] = pid_integ + (obs - ctrl[3]) * st;
             a_bolus = 0.0;
         } else {
             a_basal = a.act_basal[(int64_t)k * a.act_stride + e];
@@ -208,8 +221,8 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
                 a.counters[row * a.n + e] = cnt.nstep;
                 a.counters[(row + 1) * a.n + e] = cnt.nrej;
             }
-            s[14] += (double)cnt.nstep;
-            s[15] += (double)cnt.nrej;
+            step_nstep += cnt.nstep;
+            step_nrej += cnt.nrej;
             minute++;
             const double bg = x[12] / c(H_Vg);                          // t1dpatient.py:217-218
             if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
@@ -221,12 +234,15 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
         risk_index(CGM, t0, t1, r_now);
         const double reward = r_prev - r_now;
         const bool done = (BG < 70.0) || (BG > 350.0);                   // env.py:103
-        cgm_prev = CGM; obs = CGM; info_meal = CHO;
-        stats_add_row(s, BG, lbgi, hbgi, ri, reward, done);
+        sd[(int64_t)SD_CGM_PREV * a.cap] = CGM;
+        sd[(int64_t)SD_OBS * a.cap] = CGM;
+        sd[(int64_t)SD_INFO_MEAL * a.cap] = CHO;
+        stats_add_row_resident(a.stats + e, a.cap, BG, lbgi, hbgi, ri, reward, done, step_nstep, step_nrej);
+        step_nstep = 0; step_nrej = 0;
         if (a.trace) {
             double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
             r[0 * a.n] = BG; r[1 * a.n] = CGM; r[2 * a.n] = CHO; r[3 * a.n] = insulin;
-            r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = obs;
+            r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = CGM;
             r[8 * a.n] = reward; r[9 * a.n] = done ? 1.0 : 0.0; r[10 * a.n] = a_basal; r[11 * a.n] = a_bolus;
         }
     }
@@ -239,18 +255,11 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     sd[(int64_t)SD_LAST_FOOD * a.cap] = meal.last_food;
     sd[(int64_t)SD_H_CARRY * a.cap] = h_carry;
     sd[(int64_t)SD_LAST_CGM * a.cap] = last_cgm;
-    sd[(int64_t)SD_CGM_PREV * a.cap] = cgm_prev;
-    sd[(int64_t)SD_OBS * a.cap] = obs;
-    sd[(int64_t)SD_INFO_MEAL * a.cap] = info_meal;
-    sd[(int64_t)SD_PID_INTEG * a.cap] = pid_integ;
-    sd[(int64_t)SD_PID_PREV * a.cap] = pid_prev;
     si[(int64_t)SI_EATING * a.cap] = meal.eating;
     si[(int64_t)SI_MINUTE * a.cap] = minute;
     si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
     si[(int64_t)SI_MEAL_POS * a.cap] = meal_pos;
     si[(int64_t)SI_STATUS * a.cap] = status;
-#pragma unroll
-    for (int i = 0; i < NSTAT; i++) a.stats[(int64_t)i * a.cap + e] = s[i];
 }
 
 // T1DPatient.step (t1dpatient.py:82-116) for every episode: the patient-level seam of the reference

@@ -39,7 +39,9 @@ enum Hoisted {
     // per-thread scratch vectors of the integrator: k1 of the current step (needed again only after a
     // rejected step and by HINIT) and the two longest-lived stage accumulators (see dopri5_minute)
     H_K1, H_P7 = H_K1 + 13, H_PE = H_P7 + 13,
-    H_COUNT = H_PE + 13
+    // the accepted state y of the integrator (read once per stage, written once per accepted step)
+    H_Y = H_PE + 13,
+    H_COUNT = H_Y + 13
 };
 
 // Order of the parameter row handed over the C-ABI (include/simglucose_b200.h, sg_param).
@@ -282,11 +284,11 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     double facold = 1.0e-4;
     bool last = false, reject = false;
     int nstep = 0, naccpt = 0, idid = 0, phase = PH_K1;
-    double yt[NX], kt[NX], P3[NX], P4[NX], P5[NX], P6[NX];
+    double yt[NX], kt[NX], P4[NX], P5[NX], P6[NX];
     double h = 0.0, dnf = 0.0;
 
 #pragma unroll
-    for (int i = 0; i < NX; i++) yt[i] = y[i];
+    for (int i = 0; i < NX; i++) { yt[i] = y[i]; c.set(H_Y + i, y[i]); }
 
     // The loop condition is a warp vote: lanes whose minute is complete wait here instead of running ahead
     // into the next minute on their own (without it ptxas leaves the warp split for the rest of the episode:
@@ -304,10 +306,10 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 double dny = 0.0;
                 dnf = 0.0;
 #pragma unroll
-                for (int i = 0; i < NX; i++) { c.set(H_K1 + i, kt[i]); c.set(H_PE + i, y[i]); }
+                for (int i = 0; i < NX; i++) c.set(H_K1 + i, kt[i]);
 #pragma unroll 1
                 for (int i = 0; i < NX; i++) {               // rolled: once per minute, keep it out of the I-cache
-                    const double yi = c(H_PE + i);
+                    const double yi = c(H_Y + i);
                     const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
                     const double sk = ATOL + RTOL * fabs(yi);
                     const double a = sgm::div_r(c(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
@@ -317,7 +319,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
                 h = fmin(h, hmax);
 #pragma unroll
-                for (int i = 0; i < NX; i++) yt[i] = y[i] + h * kt[i];
+                for (int i = 0; i < NX; i++) yt[i] = c(H_Y + i) + h * kt[i];
                 phase = PH_HINIT;
             } else {
                 begin_step = true;
@@ -329,7 +331,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             for (int i = 0; i < NX; i++) c.set(H_P7 + i, kt[i]);
 #pragma unroll 1
             for (int i = 0; i < NX; i++) {
-                const double sk = ATOL + RTOL * fabs(c(H_PE + i));
+                const double sk = ATOL + RTOL * fabs(c(H_Y + i));
                 const double a = sgm::div_nr(c(H_P7 + i) - c(H_K1 + i), sk);
                 der2 = der2 + a * a;
             }
@@ -341,31 +343,33 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
             begin_step = true;
         } break;
-        case PH_S2:                                          // kt = k2
+        case PH_S2:                                          // kt = k2; the sums start here from k1 (shared memory)
 #pragma unroll
             for (int i = 0; i < NX; i++) {
-                yt[i] = y[i] + h * (P3[i] + A32 * kt[i]);
-                P4[i] = P4[i] + A42 * kt[i];
-                P5[i] = P5[i] + A52 * kt[i];
-                P6[i] = P6[i] + A62 * kt[i];
+                const double k1 = c(H_K1 + i);
+                yt[i] = c(H_Y + i) + h * (A31 * k1 + A32 * kt[i]);
+                P4[i] = A41 * k1 + A42 * kt[i];
+                P5[i] = A51 * k1 + A52 * kt[i];
+                P6[i] = A61 * k1 + A62 * kt[i];
             }
             phase = PH_S3;
             break;
         case PH_S3:                                          // kt = k3
 #pragma unroll
             for (int i = 0; i < NX; i++) {
-                yt[i] = y[i] + h * (P4[i] + A43 * kt[i]);
+                const double k1 = c(H_K1 + i);
+                yt[i] = c(H_Y + i) + h * (P4[i] + A43 * kt[i]);
                 P5[i] = P5[i] + A53 * kt[i];
                 P6[i] = P6[i] + A63 * kt[i];
-                c.set(H_P7 + i, c(H_P7 + i) + A73 * kt[i]);
-                c.set(H_PE + i, c(H_PE + i) + E3 * kt[i]);
+                c.set(H_P7 + i, A71 * k1 + A73 * kt[i]);
+                c.set(H_PE + i, E1 * k1 + E3 * kt[i]);
             }
             phase = PH_S4;
             break;
         case PH_S4:                                          // kt = k4
 #pragma unroll
             for (int i = 0; i < NX; i++) {
-                yt[i] = y[i] + h * (P5[i] + A54 * kt[i]);
+                yt[i] = c(H_Y + i) + h * (P5[i] + A54 * kt[i]);
                 P6[i] = P6[i] + A64 * kt[i];
                 c.set(H_P7 + i, c(H_P7 + i) + A74 * kt[i]);
                 c.set(H_PE + i, c(H_PE + i) + E4 * kt[i]);
@@ -375,7 +379,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         case PH_S5:                                          // kt = k5
 #pragma unroll
             for (int i = 0; i < NX; i++) {
-                yt[i] = y[i] + h * (P6[i] + A65 * kt[i]);
+                yt[i] = c(H_Y + i) + h * (P6[i] + A65 * kt[i]);
                 c.set(H_P7 + i, c(H_P7 + i) + A75 * kt[i]);
                 c.set(H_PE + i, c(H_PE + i) + E5 * kt[i]);
             }
@@ -384,7 +388,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         case PH_S6:                                          // kt = k6; yt becomes the 5th-order solution
 #pragma unroll
             for (int i = 0; i < NX; i++) {
-                yt[i] = y[i] + h * (c(H_P7 + i) + A76 * kt[i]);
+                yt[i] = c(H_Y + i) + h * (c(H_P7 + i) + A76 * kt[i]);
                 c.set(H_PE + i, c(H_PE + i) + E6 * kt[i]);
             }
             phase = PH_S7;
@@ -394,7 +398,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
 #pragma unroll
             for (int i = 0; i < NX; i++) {
                 const double e = (c(H_PE + i) + E7 * kt[i]) * h;
-                const double sk = ATOL + RTOL * sgm::max_sel(fabs(y[i]), fabs(yt[i]));
+                const double sk = ATOL + RTOL * sgm::max_sel(fabs(c(H_Y + i)), fabs(yt[i]));
                 const double a = sgm::div_nr(e, sk);
                 err = err + a * a;
             }
@@ -407,7 +411,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 facold = sgm::max_sel(err, 1.0e-4);
                 naccpt++;
 #pragma unroll
-                for (int i = 0; i < NX; i++) y[i] = yt[i];   // kt is k1 of the next step (FSAL)
+                for (int i = 0; i < NX; i++) c.set(H_Y + i, yt[i]);   // kt is k1 of the next step (FSAL)
                 x = x + h;
                 if (last) {
                     idid = 1;
@@ -440,15 +444,14 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 for (int i = 0; i < NX; i++) {
                     const double k = kt[i];
                     c.set(H_K1 + i, k);
-                    yt[i] = y[i] + ha * k;
-                    P3[i] = A31 * k; P4[i] = A41 * k; P5[i] = A51 * k; P6[i] = A61 * k;
-                    c.set(H_P7 + i, A71 * k);
-                    c.set(H_PE + i, E1 * k);
+                    yt[i] = c(H_Y + i) + ha * k;
                 }
                 phase = PH_S2;
             }
         }
     }
+#pragma unroll
+    for (int i = 0; i < NX; i++) y[i] = c(H_Y + i);
     if (carry_h) h_carry = h;
     cnt.nstep += nstep;
     return idid;
