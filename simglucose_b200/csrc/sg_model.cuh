@@ -256,6 +256,68 @@ constexpr int NMAX = 500;
 
 struct StepCount { int nstep, nrej; };
 
+// ---- pieces of the integrator that run once per minute / once per step and are kept OUT of the inlined loop
+// body (not inlined: the loop has to fit the instruction cache, see sg_math.cuh pow_pos) --------------------
+
+struct HinitGuess { double h, dnf; };
+
+// HINIT, first half: h = 0.01 * |y| / |k1| in the scaled norm.  Reads k1 (H_K1) and y (H_Y) from the column.
+template <int BLOCK>
+__device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
+{
+    const Column<BLOCK> c{col};
+    double dny = 0.0, dnf = 0.0;
+#pragma unroll 1
+    for (int i = 0; i < NX; i++) {
+        const double yi = c(H_Y + i);
+        const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
+        const double sk = ATOL + RTOL * fabs(yi);
+        const double a = sgm::div_r(c(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
+        dnf = dnf + a * a;
+        dny = dny + b * b;
+    }
+    double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+    h = fmin(h, hmax);
+    return HinitGuess{h, dnf};
+}
+
+// HINIT, second half: second-derivative estimate from f(x + h, y + h*k1) (H_P7) and k1 (H_K1).
+template <int BLOCK>
+__device__ __noinline__ double hinit_second(double *col, double h, double dnf, double hmax)
+{
+    const Column<BLOCK> c{col};
+    double der2 = 0.0;
+#pragma unroll 1
+    for (int i = 0; i < NX; i++) {
+        const double sk = ATOL + RTOL * fabs(c(H_Y + i));
+        const double a = sgm::div_nr(c(H_P7 + i) - c(H_K1 + i), sk);
+        der2 = der2 + a * a;
+    }
+    der2 = sqrt(der2) / h;
+    const double der12 = fmax(fabs(der2), sqrt(dnf));
+    const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
+    return fmin(fmin(100.0 * fabs(h), h1), hmax);
+}
+
+struct StepControl { double err, hnew_accept, hnew_reject; };
+
+// Step-size controller of DOPCOR (Lund stabilisation, beta = 0.04) from the summed squared scaled errors.
+static __device__ __noinline__ StepControl step_control(double errsum, double facold, double h)
+{
+    const double beta = 0.04, safe = 0.9;
+    const double expo1 = 0.2 - beta * 0.75;
+    const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
+    const double err = sqrt(sgm::div_nr(errsum, (double)NX));
+    const double fac11 = sgm::pow_pos(err, expo1);
+    double fac = sgm::div_nr(fac11, sgm::pow_pos(facold, beta));
+    fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
+    StepControl r;
+    r.err = err;
+    r.hnew_accept = sgm::div_nr(h, fac);
+    r.hnew_reject = sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
+    return r;
+}
+
 // One call of ode('dopri5').integrate(t + 1): k1 = f(y), HINIT (initial step size guess) unless a step
 // size is carried over, then the adaptive step loop.  Returns idid (1 ok, -2 nmax, -3 step too small).
 // h_carry: WORK(7) of the Fortran (kept across calls by scipy 1.6.3, zero in scipy >= 1.7).
@@ -274,9 +336,6 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                                              double t0, bool carry_h, double &h_carry, StepCount &cnt,
                                              unsigned lanes)
 {
-    const double beta = 0.04, safe = 0.9;
-    const double expo1 = 0.2 - beta * 0.75;
-    const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
     enum { PH_K1 = 0, PH_HINIT, PH_S2, PH_S3, PH_S4, PH_S5, PH_S6, PH_S7 };
     double x = t0;
     const double xend = t0 + 1.0;
@@ -303,21 +362,11 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         case PH_K1: {                                        // kt = k1 = f(x, y)
             h = carry_h ? h_carry : 0.0;
             if (h == 0.0) {                                  // HINIT, first half
-                double dny = 0.0;
-                dnf = 0.0;
 #pragma unroll
                 for (int i = 0; i < NX; i++) c.set(H_K1 + i, kt[i]);
-#pragma unroll 1
-                for (int i = 0; i < NX; i++) {               // rolled: once per minute, keep it out of the I-cache
-                    const double yi = c(H_Y + i);
-                    const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
-                    const double sk = ATOL + RTOL * fabs(yi);
-                    const double a = sgm::div_r(c(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
-                    dnf = dnf + a * a;
-                    dny = dny + b * b;
-                }
-                h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
-                h = fmin(h, hmax);
+                const HinitGuess g = hinit_first<BLOCK>(c.base, hmax);
+                h = g.h;
+                dnf = g.dnf;
 #pragma unroll
                 for (int i = 0; i < NX; i++) yt[i] = c(H_Y + i) + h * kt[i];
                 phase = PH_HINIT;
@@ -326,19 +375,9 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             }
         } break;
         case PH_HINIT: {                                     // kt = f(x + h, y + h*k1)
-            double der2 = 0.0;
 #pragma unroll
             for (int i = 0; i < NX; i++) c.set(H_P7 + i, kt[i]);
-#pragma unroll 1
-            for (int i = 0; i < NX; i++) {
-                const double sk = ATOL + RTOL * fabs(c(H_Y + i));
-                const double a = sgm::div_nr(c(H_P7 + i) - c(H_K1 + i), sk);
-                der2 = der2 + a * a;
-            }
-            der2 = sqrt(der2) / h;
-            const double der12 = fmax(fabs(der2), sqrt(dnf));
-            const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
-            h = fmin(fmin(100.0 * fabs(h), h1), hmax);
+            h = hinit_second<BLOCK>(c.base, h, dnf, hmax);
 #pragma unroll
             for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
             begin_step = true;
@@ -402,11 +441,9 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 const double a = sgm::div_nr(e, sk);
                 err = err + a * a;
             }
-            err = sqrt(sgm::div_nr(err, (double)NX));
-            const double fac11 = sgm::pow_pos(err, expo1);
-            double fac = sgm::div_nr(fac11, sgm::pow_pos(facold, beta));
-            fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
-            double hnew = sgm::div_nr(h, fac);
+            const StepControl sc = step_control(err, facold, h);
+            err = sc.err;
+            double hnew = sc.hnew_accept;
             if (err <= 1.0) {
                 facold = sgm::max_sel(err, 1.0e-4);
                 naccpt++;
@@ -422,7 +459,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                     begin_step = true;
                 }
             } else {
-                hnew = sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
+                hnew = sc.hnew_reject;
                 reject = true;
                 if (naccpt >= 1) cnt.nrej++;
                 last = false;

@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""Key numbers of an ncu raw page (ncu -i rep --page raw --csv > raw.csv): python tools/ncu_key.py raw.csv"""
+import csv
+import sys
+
+rows = list(csv.reader(open(sys.argv[1])))
+hdr, vals = rows[0], rows[2]
+keys = ['gpu__time_duration.sum', 'launch__registers_per_thread', 'smsp__inst_executed.sum',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active',
+        'smsp__thread_inst_executed_per_inst_executed.ratio', 'smsp__average_warp_latency_per_inst_issued.ratio',
+        'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum',
+        'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed',
+        'dram__bytes_read.sum', 'dram__bytes_write.sum']
+keys += [h for h in hdr if 'smsp__average_warps_issue_stalled' in h and 'per_issue_active' in h]
+for k in keys:
+    if k in hdr:
+        v = vals[hdr.index(k)]
+        try:
+            if float(v) == 0.0:
+                continue
+        except ValueError:
+            pass
+        print('%-90s %s' % (k.replace('smsp__average_warps_issue_stalled_', 'stall ').replace('_per_issue_active.ratio', ''), v))
