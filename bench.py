@@ -41,7 +41,8 @@ def parse():
     ap.add_argument('--steps', type=int, default=3)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--groups', type=int, default=8192, help='seed groups of 30 patients per GPU')
+    ap.add_argument('--groups', type=int, default=8840,
+                    help='seed groups of 30 patients per GPU (8840 x 30 episodes = 7 waves of 148 SMs x 256 resident threads)')
     ap.add_argument('--days', type=int, default=3)
     ap.add_argument('--fma', action='store_true', help='SG_FLAG_FMA kernels (not the default arithmetic)')
     ap.add_argument('--carry-h', action='store_true')

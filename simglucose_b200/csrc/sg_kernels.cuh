@@ -34,7 +34,7 @@ enum StateI {
 constexpr int NTRACE = 12;
 constexpr int NSTAT = 16;
 constexpr int NCTRL = 4;
-constexpr int BLOCK = 128;
+constexpr int BLOCK = 64;
 
 struct Hardware {
     int st;

@@ -1,5 +1,5 @@
 #!/bin/bash
-# Kernel-iteration session: parity tests, one resident wave (296 blocks x 128 episodes x 1 day) timed in both
+# Kernel-iteration session: parity tests, one resident wave (148 SMs x 256 resident episodes x 1 day) timed in both
 # arithmetic modes, optional ncu full capture.  Usage: bash tools/gpu_iter.sh <tag> [ncu]
 set -u
 TAG=${1:-it}; NCU=${2:-}

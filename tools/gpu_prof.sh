@@ -1,5 +1,5 @@
 #!/bin/bash
-# ncu full capture of run_kernel on one resident wave (296 blocks x 128 episodes x 1 day) + kernel-only bench.
+# ncu full capture of run_kernel on one resident wave (148 SMs x 256 resident episodes x 1 day) + kernel-only bench.
 # Usage: bash tools/gpu_prof.sh <tag> [tests] [extra bench args]
 set -u
 TAG=${1:-prof}; shift || true
