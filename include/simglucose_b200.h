@@ -244,6 +244,21 @@ int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const i
 /* out[i] ~ U(lo, hi): random basal actions (BASELINE.json configs[2]). */
 int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, uint64_t offset, void *stream);
 
+/* ---- post-hoc statistics of BG traces (simglucose/analysis/report.py), one thread per episode ----
+ * bg: element (row r, episode e) at bg[r * row_stride + e] (e.g. the BG column of an sg_run trace: row_stride =
+ * SG_NTRACE * E).  Any output may be NULL.
+ *   percent_out [5][E]            percent_stats (report.py:74-92): 70<=BG<=180, BG>180, BG<70, BG>250, BG<50
+ *   ri_out      [3][n_chunks][E]  risk_index_trace (report.py:95-133): LBGI, HBGI, RI of each chunk of chunk_rows
+ *                                 rows (the reference uses 60 rows); n_chunks = ceil(n_rows / chunk_rows)
+ *   ri_mean_out [3][E]            their means over the chunks (needs ri_out)
+ *   cvga_out    [2][E]            CVGA_analysis (report.py:198-204): 2.5 and 97.5 percentiles (numpy's linear
+ *                                 interpolation of exact order statistics), clipped to [50, 400] */
+int sg_report_stats(const double *bg, int64_t row_stride, int64_t n_rows, int64_t n_episodes, int32_t chunk_rows,
+                    double *percent_out, double *ri_out, double *ri_mean_out, double *cvga_out, void *stream);
+
+/* CVGA zone counts (report.py:206-216) over the episodes: counts_out [5] = #A, #(A or B), #C, #D, #E. */
+int sg_cvga_zones(const double *cvga, int64_t n_episodes, double *counts_out, void *stream);
+
 /* Accuracy probe of the kernel's own FP64 helpers (csrc/sg_math.cuh) against CUDA's libm, elementwise:
  * kind 0 div_nr(a,b), 1 a/b, 2 tanh_diff(a,b), 3 tanh(a)-tanh(b), 4 pow_pos(a,b), 5 pow(a,b), 6 exp_core(a),
  * 7 exp(a), 8 log_core(a), 9 log(a).  Test hook only. */

@@ -166,8 +166,48 @@ def g_noise(pool):
     print('wrote', os.path.normpath(path), flush=True)
 
 
+def g_report(pool):
+    """analysis/report.py (percent_stats :74-92, risk_index_trace :95-133, CVGA_analysis :198-217) run by the
+    reference's own code on the BG traces of the cohort fixtures (plotting calls made inert)."""
+    H._activate()
+    import pandas as pd
+    pd.DataFrame.plot = lambda self, *a, **k: None          # no matplotlib in the build container
+    from simglucose.analysis import report as R
+
+    class _NumpyCompat(object):
+        """np.mean(DataFrame) is the per-column mean under the reference's pinned pandas 1.2.4 (it calls
+        DataFrame.mean()); pandas >= 2 reduces over both axes.  Everything else is numpy itself."""
+        def __getattr__(self, name):
+            return getattr(np, name)
+
+        @staticmethod
+        def mean(a, *args, **kw):
+            return a.mean() if isinstance(a, pd.DataFrame) else np.mean(a, *args, **kw)
+    R.np = _NumpyCompat()
+    out = {}
+    for tag, fixture in (('bb', 'cohort_bb_3day'), ('pid', 'cohort_pid_1day')):
+        d = np.load(os.path.join(OUT, fixture + '.npz'))
+        n = 30
+        BG = pd.DataFrame(d['BG'][:n].T, columns=H.patient_names()[:n])        # [time x patient], as df.unstack(level=0).BG
+        pstats, _, _ = R.percent_stats(BG)
+        ri_per_hour, ri_mean, _, _ = R.risk_index_trace(BG, visualize=False)
+        BG_min, BG_max, A, B, C, D_, E = R.CVGA_analysis(BG)
+        out[tag + '_BG'] = BG.to_numpy(float)
+        out[tag + '_percent'] = pstats.to_numpy(float)                          # [patient x 5]
+        out[tag + '_percent_cols'] = np.array(list(pstats.columns))
+        out[tag + '_ri_per_hour'] = ri_per_hour.to_numpy(float)                 # [(metric, patient) x chunk]
+        out[tag + '_ri_mean'] = ri_mean.to_numpy(float)                         # [patient x 3]
+        out[tag + '_ri_mean_cols'] = np.array(list(ri_mean.columns))
+        out[tag + '_cvga_min'] = np.asarray(BG_min, float)
+        out[tag + '_cvga_max'] = np.asarray(BG_max, float)
+        out[tag + '_zones'] = np.array([A, B, C, D_, E], dtype=float)
+    path = os.path.join(OUT, 'report_stats.npz')
+    np.savez_compressed(path, **out)
+    print('wrote', os.path.normpath(path), '%.1f KB' % (os.path.getsize(path) / 1024.0), flush=True)
+
+
 GROUPS = dict(golden_config=g_golden_config, custom=g_custom, cohort_bb=g_cohort_bb, cohort_pid=g_cohort_pid,
-              open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise)
+              open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise, report=g_report)
 
 if __name__ == '__main__':
     groups = sys.argv[1:] or list(GROUPS)

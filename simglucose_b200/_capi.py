@@ -33,6 +33,7 @@ SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_har
            'sg_reduce_stats', 'sg_num_episodes', 'sg_launch_count',
            'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_patient_step', 'sg_model', 'sg_pump',
            'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
+           'sg_report_stats', 'sg_cvga_zones',
            'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma']
 
 
@@ -79,6 +80,8 @@ def load():
     L.sg_get_episode_state.argtypes = [vp, dp, ip, vp]
     L.sg_set_episode_state.argtypes = [vp, dp, ip, C.c_int64, vp]
     L.sg_math_probe.argtypes = [C.c_int32, dp, dp, dp, C.c_int64, vp]
+    L.sg_report_stats.argtypes = [dp, C.c_int64, C.c_int64, C.c_int64, C.c_int32, dp, dp, dp, dp, vp]
+    L.sg_cvga_zones.argtypes = [dp, C.c_int64, dp, vp]
     L.sg_get_state.argtypes = [vp, dp, vp]
     L.sg_get_stats.argtypes = [vp, dp, vp]
     L.sg_get_status.argtypes = [vp, ip, vp]
