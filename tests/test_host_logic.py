@@ -219,8 +219,12 @@ print('rank', rank, 'ok')
 def test_stats_allreduce_over_gloo_world_size_2(tmp_path):
     script = tmp_path / 'worker.py'
     script.write_text(_GLOO_WORKER % {'root': ROOT})
+    import socket
+    with socket.socket() as sk:                           # a free rendezvous port on the loopback interface
+        sk.bind(('127.0.0.1', 0))
+        port = sk.getsockname()[1]
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2', '--master-addr', '127.0.0.1',
-           '--master-port', '29641', str(script)]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+           '--master-port', str(port), str(script)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert 'rank 0 ok' in r.stdout and 'rank 1 ok' in r.stdout
