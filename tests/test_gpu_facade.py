@@ -347,3 +347,28 @@ def test_vector_env_device_streams():
     assert torch.equal(a.state, b.state)
     assert torch.isfinite(out[:, T('BG')]).all()
     a.close(); b.close()
+
+
+def test_simulate_keyword_interface(tmp_path):
+    """user_interface.simulate(...) with every argument given (tests/test_ui.py of the reference drives the same
+    call through mocked prompts): per-patient CSVs + the three report CSVs; numbers == the cohort fixture."""
+    import pandas as pd
+    from simglucose_b200.controller.basal_bolus_ctrller import BBController
+    from simglucose_b200.simulation.scenario_gen import RandomScenario
+    from simglucose_b200.simulation.user_interface import simulate
+    d = H.load('cohort_bb_3day')
+    names = [_names()[i] for i in (0, 12, 25)]
+    start = datetime(2018, 1, 1, 0, 0, 0)
+    res = simulate(sim_time=timedelta(days=3), scenario=RandomScenario(start_time=start, seed=1), controller=BBController(),
+                   patient_names=names, cgm_name='Dexcom', cgm_seed=1, insulin_pump_name='Insulet', start_time=start,
+                   save_path=str(tmp_path), animate=False, parallel=True)
+    assert list(res.index) == names and res.shape == (3, 8)
+    for j, i in enumerate((0, 12, 25)):
+        back = pd.read_csv(os.path.join(str(tmp_path), names[j] + '.csv'))
+        assert H.rel_err(back['BG'].to_numpy(), d['BG'][i]) <= TOL
+        bg = d['BG'][i]
+        assert abs(res.iloc[j]['BG>180'] - (bg > 180).sum() / len(bg) * 100) <= 100.0 / len(bg) + 1e-9
+    for f in ('performance_stats.csv', 'risk_trace.csv', 'CVGA_stats.csv'):
+        assert os.path.exists(os.path.join(str(tmp_path), f))
+    with pytest.raises(ValueError):
+        simulate(sim_time=timedelta(days=1))

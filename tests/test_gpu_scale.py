@@ -1,0 +1,132 @@
+"""GPU: BASELINE.json-sized populations checked through size-independent properties (the oracle cannot follow
+at these sizes): determinism, independence of episodes from their batch and shard, fused == lockstep,
+population aggregate == reduction of the per-episode statistics, oracle spot checks on sampled episodes.
+
+Sizes: configs[2] 1,048,576 lockstep episodes (a few env-steps), configs[4] 30 x 10,000 seeds x 1 day (fused),
+configs[3] perturbed parameters (262,144 episodes, half a day)."""
+import numpy as np
+import pytest
+
+import helpers as H
+from helpers import O
+
+pytestmark = pytest.mark.gpu
+
+
+def _cohort_inputs(E, n_steps, seed, offset=0, group=30, dev=None):
+    import torch
+    from simglucose_b200 import streams as S
+    dev = dev or torch.device('cuda', 0)
+    rows = ((torch.arange(E, device=dev, dtype=torch.int64) + offset) % 30).to(torch.int32)
+    noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=seed, episode_offset=offset, group_size=group, device=dev)
+    mm, mg = S.device_scenarios(E, n_steps * 3, start_minute=0, seed=seed, episode_offset=offset, group_size=group, device=dev)
+    return rows, noise, mm, mg
+
+
+def test_config4_size_pid_population_properties():
+    """30 patients x 10,000 seeds x 1 day, PID fused (BASELINE.json configs[4])."""
+    import torch
+    from simglucose_b200.engine import BatchEngine
+    E, n_steps = 300000, 480
+    rows, noise, mm, mg = _cohort_inputs(E, n_steps, seed=0)
+    eng = BatchEngine(E)
+    pid = (1e-3, 1e-5, 1e-3, 140.0)
+    eng.reset(rows, noise, mm, mg, row0=False)
+    eng.run(n_steps, controller='pid', ctrl=pid, trace=False)
+    st = eng.stats().clone()
+    agg = eng.reduce_stats().cpu().numpy()
+    status = eng.status()
+    assert int((status != 1).sum()) == 0
+    s = st.cpu().numpy()
+    assert np.all(np.isfinite(s))
+    assert agg[0] == E * (n_steps + 1) == s[0].sum()
+    assert agg[2] == s[2].min() and agg[3] == s[3].max() and agg[13] == (s[13] >= 0).sum()
+    for k in (8, 9, 10, 11, 12, 14, 15):                         # integer counters: exact sums
+        assert agg[k] == s[k].sum()
+    for k in (1, 4, 5, 6, 7):
+        assert abs(agg[k] - s[k].sum()) <= 1e-9 * max(1.0, abs(s[k].sum()))
+    # determinism: the same launch again gives identical bits
+    eng.reset(rows, noise, mm, mg, row0=False)
+    eng.run(n_steps, controller='pid', ctrl=pid, trace=False)
+    assert torch.equal(eng.stats(), st)
+    # shard independence: episodes [lo, hi) simulated alone (another rank's view) == the same episodes in the big batch
+    lo, hi = 123450, 123450 + 6000
+    r2, n2, m2, g2 = _cohort_inputs(hi - lo, n_steps, seed=0, offset=lo)
+    small = BatchEngine(hi - lo)
+    small.reset(r2, n2, m2, g2, row0=False)
+    out = small.run(n_steps, controller='pid', ctrl=pid, trace=True)
+    assert torch.equal(small.stats(), st[:, lo:hi])
+    # oracle spot checks on sampled episodes of the shard
+    tr = out['trace'].cpu().numpy()
+    nz, mmh, mgh = n2.cpu().numpy(), m2.cpu().numpy(), g2.cpu().numpy()
+    for j in (0, 1777, 5999):
+        row = int(r2[j])
+        p, x0 = O.patient_params(row)
+        k = mmh[:, j] >= 0
+        o = O.run_episode(p, x0, n_steps, mmh[k, j], mgh[k, j], nz[:, j], controller='pid', ctrl=pid)
+        assert H.rel_err(tr[:, 0, j], o['BG'][1:]) <= H.REL_TOL
+        assert np.array_equal(tr[:, 9, j] != 0, o['done'][1:] != 0)
+    small.close()
+    eng.close()
+
+
+def test_config2_size_lockstep_equals_fused():
+    """1,048,576 environments stepped in lockstep (one launch per env-step) == the fused episode kernel."""
+    import torch
+    from simglucose_b200 import streams as S
+    from simglucose_b200.engine import BatchEngine
+    E, n_steps = 1048576, 6
+    rows, noise, mm, mg = _cohort_inputs(E, n_steps, seed=3, group=1)
+    acts = torch.stack([S.device_uniform(E, 0.0, 0.05, seed=0, offset=k * E) for k in range(n_steps)])
+    zeros = torch.zeros_like(acts[0])
+    a = BatchEngine(E)
+    a.reset(rows, noise, mm, mg, row0=False)
+    last = None
+    for k in range(n_steps):
+        last = a.step(acts[k], zeros)
+    b = BatchEngine(E)
+    b.reset(rows, noise, mm, mg, row0=False)
+    full = torch.stack([acts, torch.zeros_like(acts)], dim=1).contiguous()
+    out = b.run(n_steps, controller='actions', actions=full, trace=True)['trace']
+    assert torch.equal(out[-1], last)
+    assert torch.equal(a.state(), b.state()) and torch.equal(a.stats(), b.stats())
+    assert float(acts.min()) >= 0.0 and float(acts.max()) <= 0.05 and abs(float(acts.mean()) - 0.025) < 1e-4
+    a.close(); b.close()
+
+
+def test_config3_size_perturbed_population():
+    """+-10 % parameter perturbation (BASELINE.json configs[3]): bounds, determinism, table rows unperturbed at
+    amplitude 0, every solver status ok over half a day with BBController."""
+    import torch
+    from simglucose_b200 import params as P, streams as S
+    from simglucose_b200.engine import BatchEngine
+    E, n_steps = 262144, 240
+    rows, noise, mm, mg = _cohort_inputs(E, n_steps, seed=1234, group=1)
+    tbl = torch.from_numpy(P.cohort_table()[0]).cuda()
+    pp = S.device_perturbed_params(rows, amplitude=0.1, seed=1234)
+    base = tbl[rows.long()].T
+    ratio = (pp / base).cpu().numpy()
+    assert ratio.min() >= 0.9 - 1e-12 and ratio.max() <= 1.1 + 1e-12 and abs(ratio.mean() - 1.0) < 1e-3
+    assert torch.equal(S.device_perturbed_params(rows, amplitude=0.1, seed=1234), pp)
+    assert torch.equal(S.device_perturbed_params(rows, amplitude=0.0, seed=1234), base.contiguous())
+    q = torch.from_numpy(P.quest_table()).cuda()[rows.long()]
+    ctrl_rows = torch.stack([torch.full_like(q[:, 0], 140.0), q[:, 0], q[:, 1], torch.zeros_like(q[:, 0])]).contiguous()
+    eng = BatchEngine(E)
+    eng.reset(rows, noise, mm, mg, params=pp, row0=False)
+    out = eng.run(n_steps, controller='bb', ctrl_rows=ctrl_rows, trace=False)
+    assert int((eng.status() != 1).sum()) == 0
+    st = eng.stats().cpu().numpy()
+    assert np.all(np.isfinite(st)) and st[0].min() == n_steps + 1
+    # oracle spot check with the perturbed parameter rows
+    pph, nz, mmh, mgh = pp.cpu().numpy(), noise.cpu().numpy(), mm.cpu().numpy(), mg.cpu().numpy()
+    x0 = P.cohort_table()[1]
+    qh = P.quest_table()
+    for j in (5, 131071, 262143):
+        r = int(rows[j])
+        k = mmh[:, j] >= 0
+        o = O.run_episode(pph[:, j], x0[r], n_steps, mmh[k, j], mgh[k, j], nz[:, j], controller='bb',
+                          ctrl=(140.0, qh[r, 0], qh[r, 1]))
+        ref = np.array([o['stats'][c] for c in O.STAT_COLS])
+        assert np.array_equal(st[[0, 8, 9, 10, 11, 12, 13, 14, 15], j], ref[[0, 8, 9, 10, 11, 12, 13, 14, 15]])
+        assert abs(st[1, j] - ref[1]) <= 1e-6 * abs(ref[1])
+    eng.close()
