@@ -31,7 +31,7 @@ FLAG_CARRY_H, FLAG_FMA = 1, 2
 SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_hardware', 'sg_load_params',
            'sg_reset', 'sg_step', 'sg_run', 'sg_get_state', 'sg_get_stats', 'sg_get_status',
            'sg_reduce_stats', 'sg_num_episodes', 'sg_launch_count',
-           'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_patient_step', 'sg_model', 'sg_pump',
+           'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_set_step_cap', 'sg_patient_step', 'sg_model', 'sg_pump',
            'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
            'sg_report_stats', 'sg_cvga_zones',
            'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma']
@@ -71,6 +71,7 @@ def load():
     L.sg_step_meals.argtypes = [vp, dp, dp, dp, dp, vp]
     L.sg_rebind_streams.argtypes = [vp, ip, dp, C.c_int32, dp, C.c_int64]
     L.sg_set_t0.argtypes = [vp, C.c_int32]
+    L.sg_set_step_cap.argtypes = [vp, C.c_int32]
     L.sg_patient_step.argtypes = [vp, dp, dp, dp, vp]
     L.sg_model.argtypes = [vp, C.c_int64, dp, dp, dp, dp, dp, ip, dp, dp, vp]
     L.sg_pump.argtypes = [dp, dp, C.c_int64, C.c_double, C.c_double, C.c_double, vp]

@@ -53,6 +53,10 @@ struct sg_context {
     bool is_reset = false;
     int32_t t0 = 0;
     int64_t launches = 0;
+    // heavy minutes put aside (sg_set_step_cap)
+    int32_t step_cap = 0;
+    double *defer_d = nullptr;
+    int32_t *defer_i = nullptr, *defer_list = nullptr, *defer_count = nullptr;
 };
 
 namespace {
@@ -79,6 +83,8 @@ sgk::EpisodeArgs base_args(const sg_context *h)
     a.noise = h->noise; a.n_noise = h->n_noise;
     a.hw = h->hw;
     a.carry_h = (h->flags & SG_FLAG_CARRY_H) ? 1 : 0;
+    a.step_cap = h->step_cap;
+    a.defer_d = h->defer_d; a.defer_i = h->defer_i; a.defer_list = h->defer_list; a.defer_count = h->defer_count;
     return a;
 }
 
@@ -123,6 +129,7 @@ int sg_destroy(sg_handle h)
     DeviceGuard g(h->device);
     cudaFree(h->sd); cudaFree(h->si); cudaFree(h->stats); cudaFree(h->partials);
     cudaFree(h->table); cudaFree(h->table_x0);
+    cudaFree(h->defer_d); cudaFree(h->defer_i); cudaFree(h->defer_list); cudaFree(h->defer_count);
     delete h;
     return SG_OK;
 }
@@ -199,6 +206,22 @@ static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, co
     a.act_basal = basal; a.act_bolus = bolus; a.act_stride = act_stride;
     a.n_steps = n_steps;
     a.trace = trace; a.counters = counters; a.step_meals = step_meals;
+    if (h->step_cap > 0) {
+        // one env-step per launch pair: phase A puts heavy minutes aside, phase B finishes them in full warps
+        for (int32_t k = 0; k < n_steps; k++) {
+            sgk::EpisodeArgs b = a;
+            b.n_steps = 1;
+            if (basal) { b.act_basal = basal + (int64_t)k * act_stride; b.act_bolus = bolus + (int64_t)k * act_stride; }
+            if (trace) b.trace = trace + (int64_t)k * sgk::NTRACE * h->n;
+            if (counters) b.counters = counters + (int64_t)k * h->hw.st * 2 * h->n;
+            cudaError_t ce = use_fma(h) ? sg_fma::launch_run_capped(b, (cudaStream_t)stream)
+                                        : sg_strict::launch_run_capped(b, (cudaStream_t)stream);
+            if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
+            h->launches += 2;
+        }
+        h->steps_done += n_steps;
+        return SG_OK;
+    }
     cudaError_t ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream)
                                 : sg_strict::launch_run(a, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
@@ -244,6 +267,22 @@ int sg_rebind_streams(sg_handle h, const int32_t *meal_minute, const double *mea
     if (!noise || n_noise < h->steps_done + 2) return fail(SG_ERR_ARG, "sg_rebind_streams: noise stream shorter than what was consumed");
     h->meal_minute = meal_minute; h->meal_grams = meal_grams; h->max_meals = max_meals;
     h->noise = noise; h->n_noise = n_noise;
+    return SG_OK;
+}
+
+int sg_set_step_cap(sg_handle h, int32_t cap)
+{
+    if (!h || cap < 0) return fail(SG_ERR_ARG, "sg_set_step_cap: bad arguments");
+    if (cap > 0 && cap < 4) return fail(SG_ERR_ARG, "sg_set_step_cap: a cap below 4 steps would put ordinary minutes aside");
+    DeviceGuard g(h->device);
+    if (cap > 0 && !h->defer_d) {
+        cudaError_t ce = cudaMalloc(&h->defer_d, sizeof(double) * sgk::DEFER_ND * h->cap);
+        if (ce == cudaSuccess) ce = cudaMalloc(&h->defer_i, sizeof(int32_t) * sgk::DEFER_NI * h->cap);
+        if (ce == cudaSuccess) ce = cudaMalloc(&h->defer_list, sizeof(int32_t) * h->cap);
+        if (ce == cudaSuccess) ce = cudaMalloc(&h->defer_count, sizeof(int32_t));
+        if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_step_cap: cudaMalloc", ce);
+    }
+    h->step_cap = cap;
     return SG_OK;
 }
 

@@ -132,12 +132,17 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
     }
 }
 
-__global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
+// MODE RUN_PLAIN: every minute is integrated to its end by the lane that owns the episode.
+// MODE RUN_CAPPED (phase A of sg_set_step_cap, one env-step per launch): a minute that needs more than step_cap DOPRI5
+//   steps is put aside -- integrator state to the defer scratch, episode appended to defer_list -- and the lane
+//   idles for the rest of the env-step, so its warp is not held up.
+// MODE RUN_RESUME (phase B): one thread per entry of defer_list finishes that minute and the rest of the env-step.
+enum RunMode { RUN_PLAIN = 0, RUN_CAPPED = 1, RUN_RESUME = 2 };
+
+template <int MODE>
+__device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_t e, const unsigned lanes, double *smem)
 {
-    extern __shared__ double smem[];   // H_COUNT rows x BLOCK columns
-    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
-    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);   // the lanes that own an episode
-    if (e >= a.n) return;          // no block-level synchronisation below: columns are private
+    constexpr bool DEFER = MODE != RUN_PLAIN;
     const Column<BLOCK> c{smem + threadIdx.x};
     const ParamLoad p = param_source(a, e);
     stage_params(c, p);
@@ -167,14 +172,36 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     const double st = (double)st_i;
     int next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
 
+    // ---- minute put aside (phases A / B) ----
+    Suspend sp{0.0, 0.0, 0.0, 0, 0, 0, 0};
+    int j0 = 0;                                        // RUN_RESUME: the minute of the env-step to resume at
+    double r_ins = 0.0, r_announced = 0.0, r_CHO = 0.0, r_insulin = 0.0, r_BG = 0.0, r_CGM = 0.0;
+    if (MODE == RUN_RESUME) {
+        const double *dd = a.defer_d + e;
+        const int32_t *di = a.defer_i + e;
+#pragma unroll
+        for (int i = 0; i < NX; i++) c.set(H_K1 + i, dd[(int64_t)i * a.cap]);
+        sp.h = dd[(int64_t)13 * a.cap]; sp.x = dd[(int64_t)14 * a.cap]; sp.facold = dd[(int64_t)15 * a.cap];
+        r_ins = dd[(int64_t)16 * a.cap]; r_announced = dd[(int64_t)17 * a.cap];
+        r_CHO = dd[(int64_t)18 * a.cap]; r_insulin = dd[(int64_t)19 * a.cap];
+        r_BG = dd[(int64_t)20 * a.cap]; r_CGM = dd[(int64_t)21 * a.cap];
+        sp.nstep = di[(int64_t)0 * a.cap]; sp.naccpt = di[(int64_t)1 * a.cap]; sp.nrej = di[(int64_t)2 * a.cap];
+        sp.reject = di[(int64_t)3 * a.cap]; j0 = di[(int64_t)4 * a.cap];
+        step_nstep = di[(int64_t)5 * a.cap]; step_nrej = di[(int64_t)6 * a.cap];
+    }
+
     for (int k = 0; k < a.n_steps; k++) {
         // ---- controller.policy(observation, reward, done, **info) ----
-        double a_basal, a_bolus;
+        double a_basal = 0.0, a_bolus = 0.0;
+        double ins, CHO = 0.0, insulin = 0.0, BG = 0.0, CGM = 0.0;
+        const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
+        if (MODE == RUN_RESUME) {
+            ins = r_ins; CHO = r_CHO; insulin = r_insulin; BG = r_BG; CGM = r_CGM;
+        } else {
         double ctrl[NCTRL];                            // re-read per env-step (L2 resident): not live across the integrator
 #pragma unroll
         for (int i = 0; i < NCTRL; i++) ctrl[i] = a.ctrl_rows ? __ldg(a.ctrl_rows + (int64_t)i * a.n + e) : a.ctrl[i];
         const double obs = sd[(int64_t)SD_OBS * a.cap];
-        const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
         if (a.controller == 1) {                       // BBController._bb_policy
             const double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
             a_basal = __ldg(&p.base[P_u2ss * p.stride]) * c(H_BW) / 6000.0;
@@ -197,12 +224,24 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
             a_bolus = a.act_bolus[(int64_t)k * a.act_stride + e];
         }
         // ---- env.step, env.py:66-117 ----
-        const double ins = pump_quantise(a_basal, a.hw.pump[0], a.hw.pump[1], a.hw.pump[2]) +
-                           pump_quantise(a_bolus, a.hw.pump[3], a.hw.pump[4], a.hw.pump[5]);
-        double CHO = 0.0, insulin = 0.0, BG = 0.0, CGM = 0.0;
+        ins = pump_quantise(a_basal, a.hw.pump[0], a.hw.pump[1], a.hw.pump[2]) +
+              pump_quantise(a_bolus, a.hw.pump[3], a.hw.pump[4], a.hw.pump[5]);
+        if (a.trace) {                                 // the action columns of the history row
+            double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
+            r[10 * a.n] = a_basal; r[11 * a.n] = a_bolus;
+        }
+        }
+        bool aside = false;                            // RUN_CAPPED: this lane's minute was put aside
         for (int j = 0; j < st_i; j++) {               // mini_step, env.py:48-64
+            int mode = MINUTE_FRESH;
+            if (MODE == RUN_CAPPED && aside) mode = MINUTE_IDLE;
+            if (MODE == RUN_RESUME) mode = (j < j0) ? MINUTE_IDLE : (j == j0 ? MINUTE_RESUME : MINUTE_FRESH);
             double announced = 0.0;
-            if (a.step_meals) {                        // scenario.get_action evaluated by the caller
+            if (DEFER && mode == MINUTE_IDLE) {
+                // nothing to prepare
+            } else if (DEFER && mode == MINUTE_RESUME) {
+                announced = r_announced;               // the meal machine already ran for this minute
+            } else if (a.step_meals) {                 // scenario.get_action evaluated by the caller
                 announced = a.step_meals[(int64_t)j * a.n + e];
             } else {
                 while (next_mm >= 0 && next_mm < minute) {
@@ -211,10 +250,33 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
                 }
                 if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
             }
-            const double to_eat = meal_machine(meal, announced, x[0], x[1]);
-            const Minute m = minute_setup(c, to_eat, ins, meal.last_Qsto, meal.last_food);
+            Minute m{0.0, 0.0, false};
+            if (!DEFER || mode != MINUTE_IDLE) {
+                const double to_eat = (DEFER && mode == MINUTE_RESUME) ? meal.last_cho
+                                                                        : meal_machine(meal, announced, x[0], x[1]);
+                m = minute_setup(c, to_eat, ins, meal.last_Qsto, meal.last_food);
+            }
             StepCount cnt{0, 0};
-            const int idid = dopri5_minute(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt, lanes);
+            const int idid = dopri5_minute<BLOCK, DEFER>(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt, lanes,
+                                                         mode, MODE == RUN_CAPPED ? a.step_cap : 0, &sp);
+            if (DEFER && mode == MINUTE_IDLE) continue;
+            if (MODE == RUN_CAPPED && idid == IDID_SUSPENDED) {
+                // ---- put the rest of the env-step aside for phase B ----
+                aside = true;
+                double *dd = a.defer_d + e;
+                int32_t *di = a.defer_i + e;
+#pragma unroll
+                for (int i = 0; i < NX; i++) dd[(int64_t)i * a.cap] = c(H_K1 + i);
+                dd[(int64_t)13 * a.cap] = sp.h; dd[(int64_t)14 * a.cap] = sp.x; dd[(int64_t)15 * a.cap] = sp.facold;
+                dd[(int64_t)16 * a.cap] = ins; dd[(int64_t)17 * a.cap] = announced;
+                dd[(int64_t)18 * a.cap] = CHO; dd[(int64_t)19 * a.cap] = insulin;
+                dd[(int64_t)20 * a.cap] = BG; dd[(int64_t)21 * a.cap] = CGM;
+                di[(int64_t)0 * a.cap] = sp.nstep; di[(int64_t)1 * a.cap] = sp.naccpt; di[(int64_t)2 * a.cap] = sp.nrej;
+                di[(int64_t)3 * a.cap] = sp.reject; di[(int64_t)4 * a.cap] = j;
+                di[(int64_t)5 * a.cap] = step_nstep; di[(int64_t)6 * a.cap] = step_nrej;
+                a.defer_list[atomicAdd(a.defer_count, 1)] = (int32_t)e;
+                continue;
+            }
             if (idid < 0 && status > 0) status = idid;
             if (a.counters) {
                 const int64_t row = (int64_t)(k * st_i + j) * 2;
@@ -228,6 +290,7 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
             if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
             CHO += announced / st; insulin += ins / st; BG += bg / st; CGM += last_cgm / st;
         }
+        if (MODE == RUN_CAPPED && aside) continue;     // phase B closes this env-step
         double lbgi, hbgi, ri, r_prev, r_now, t0, t1;
         risk_index(BG, lbgi, hbgi, ri);                                  // env.py:85
         risk_index(cgm_prev, t0, t1, r_prev);                            // risk_diff, env.py:27-33
@@ -243,7 +306,7 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
             double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
             r[0 * a.n] = BG; r[1 * a.n] = CGM; r[2 * a.n] = CHO; r[3 * a.n] = insulin;
             r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = CGM;
-            r[8 * a.n] = reward; r[9 * a.n] = done ? 1.0 : 0.0; r[10 * a.n] = a_basal; r[11 * a.n] = a_bolus;
+            r[8 * a.n] = reward; r[9 * a.n] = done ? 1.0 : 0.0;
         }
     }
 
@@ -260,6 +323,36 @@ __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
     si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
     si[(int64_t)SI_MEAL_POS * a.cap] = meal_pos;
     si[(int64_t)SI_STATUS * a.cap] = status;
+}
+
+__global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
+{
+    extern __shared__ double smem[];   // H_COUNT rows x BLOCK columns
+    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);   // the lanes that own an episode
+    if (e >= a.n) return;          // no block-level synchronisation below: columns are private
+    episode_steps<RUN_PLAIN>(a, e, lanes, smem);
+}
+
+__global__ void __launch_bounds__(BLOCK) run_capped_kernel(const EpisodeArgs a)
+{
+    extern __shared__ double smem[];
+    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);
+    if (e >= a.n) return;
+    episode_steps<RUN_CAPPED>(a, e, lanes, smem);
+}
+
+// Phase B: grid-stride over the episodes that phase A put aside (every warp is full of heavy minutes).
+__global__ void __launch_bounds__(BLOCK) run_resume_kernel(const EpisodeArgs a)
+{
+    extern __shared__ double smem[];
+    const int count = *a.defer_count;
+    for (int64_t base = (int64_t)blockIdx.x * BLOCK; base < count; base += (int64_t)gridDim.x * BLOCK) {
+        const int64_t idx = base + threadIdx.x;
+        const unsigned lanes = __ballot_sync(0xffffffffu, idx < count);
+        if (idx < count) episode_steps<RUN_RESUME>(a, (int64_t)a.defer_list[idx], lanes, smem);
+    }
 }
 
 // T1DPatient.step (t1dpatient.py:82-116) for every episode: the patient-level seam of the reference
@@ -488,6 +581,28 @@ cudaError_t launch_run(const EpisodeArgs &a, cudaStream_t s)
         configured = true;
     }
     run_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
+    return cudaGetLastError();
+}
+
+// One env-step with heavy minutes put aside: counter reset, phase A over all episodes, phase B over the list.
+cudaError_t launch_run_capped(const EpisodeArgs &a, cudaStream_t s)
+{
+    constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(run_capped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(run_resume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    cudaError_t e = cudaMemsetAsync(a.defer_count, 0, sizeof(int32_t), s);
+    if (e != cudaSuccess) return e;
+    run_capped_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    unsigned blocks = grid_for(a.n);
+    if (blocks > 148u * 4u) blocks = 148u * 4u;            // one resident wave; the kernel strides over the list
+    run_resume_kernel<<<blocks, BLOCK, kSmem, s>>>(a);
     return cudaGetLastError();
 }
 

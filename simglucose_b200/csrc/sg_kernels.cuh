@@ -35,6 +35,10 @@ constexpr int NTRACE = 12;
 constexpr int NSTAT = 16;
 constexpr int NCTRL = 4;
 constexpr int BLOCK = 64;
+// scratch rows of an episode whose minute was put aside: k1[13], h, x, facold, ins, announced, CHO, insulin, BG, CGM
+constexpr int DEFER_ND = 22;
+// nstep, naccpt, nrej, reject, minute index inside the env-step, steps / rejects of the env-step so far
+constexpr int DEFER_NI = 7;
 
 struct Hardware {
     int st;
@@ -72,6 +76,12 @@ struct EpisodeArgs {
     const double *step_meals;  // [st][n] grams announced in each minute of a single step (n_steps == 1), or null: table
     double *trace;             // [n_steps][NTRACE][n] or null
     int32_t *counters;         // [n_steps*st][2][n] or null
+    // heavy minutes put aside (sg_set_step_cap): phase A fills, phase B consumes
+    int32_t step_cap;          // DOPRI5 steps after which a minute is put aside; 0 = never
+    double *defer_d;           // [DEFER_ND][cap]
+    int32_t *defer_i;          // [DEFER_NI][cap]
+    int32_t *defer_list;       // [cap] episodes put aside by the last phase A launch
+    int32_t *defer_count;      // [1]
     // reset
     const double *x0;          // [13][n] or null
     double *row0;              // [NTRACE][n] or null
@@ -118,6 +128,7 @@ struct ReduceArgs {
     namespace NS {                                                            \
     cudaError_t launch_reset(const sgk::EpisodeArgs &a, cudaStream_t s);      \
     cudaError_t launch_run(const sgk::EpisodeArgs &a, cudaStream_t s);        \
+    cudaError_t launch_run_capped(const sgk::EpisodeArgs &a, cudaStream_t s); \
     cudaError_t launch_reduce(const sgk::ReduceArgs &a, cudaStream_t s);      \
     cudaError_t launch_patient_step(const sgk::PatientArgs &a, cudaStream_t s); \
     cudaError_t launch_model(const sgk::ModelArgs &a, cudaStream_t s);        \

@@ -256,6 +256,16 @@ constexpr int NMAX = 500;
 
 struct StepCount { int nstep, nrej; };
 
+// Integrator state of a minute that was put aside at the beginning of a DOPRI5 step (heavy minutes -- a meal onset
+// costs up to 36 steps against 3 -- are finished by a second kernel over the compacted list of such episodes, so
+// that the other 31 lanes of the warp do not wait for them).  k1 of the step travels in the H_K1 slots.
+struct Suspend {
+    double h, x, facold;
+    int nstep, naccpt, nrej, reject;
+};
+enum MinuteMode { MINUTE_IDLE = 0, MINUTE_FRESH = 1, MINUTE_RESUME = 2 };
+constexpr int IDID_SUSPENDED = 2;
+
 // ---- pieces of the integrator that run once per minute / once per step and are kept OUT of the inlined loop
 // body (not inlined: the loop has to fit the instruction cache, see sg_math.cuh pow_pos) --------------------
 
@@ -331,23 +341,37 @@ static __device__ __noinline__ StepControl step_control(double errsum, double fa
 //     sequence of roundings as  a_s1*k1 + a_s2*k2 + ...  and leaves no k -> register copies.  P3..P6 live in
 //     registers; the two longest-lived sums (stage 7 and the error estimator) live in the thread's
 //     shared-memory column together with k1, which is needed again only by HINIT and after a rejection.
-template <int BLOCK>
+//
+// DEFER (compile time): mode selects what this lane does in the call -- MINUTE_FRESH a whole minute, MINUTE_IDLE
+// nothing (it only takes part in the warp votes), MINUTE_RESUME the rest of a minute put aside earlier (sp, k1 in
+// H_K1); with cap > 0 a minute that is about to start its (cap+1)-th step is put aside: sp and H_K1 are filled
+// and IDID_SUSPENDED is returned.
+template <int BLOCK, bool DEFER = false>
 __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minute &m, double (&y)[NX],
                                              double t0, bool carry_h, double &h_carry, StepCount &cnt,
-                                             unsigned lanes)
+                                             unsigned lanes, int mode = MINUTE_FRESH, int cap = 0,
+                                             Suspend *sp = nullptr)
 {
-    enum { PH_K1 = 0, PH_HINIT, PH_S2, PH_S3, PH_S4, PH_S5, PH_S6, PH_S7 };
+    enum { PH_K1 = 0, PH_HINIT, PH_S2, PH_S3, PH_S4, PH_S5, PH_S6, PH_S7, PH_RESUME };
     double x = t0;
     const double xend = t0 + 1.0;
-    const double hmax = fabs(xend - x);
+    const double hmax = fabs(xend - t0);
     double facold = 1.0e-4;
     bool last = false, reject = false;
     int nstep = 0, naccpt = 0, idid = 0, phase = PH_K1;
     double yt[NX], kt[NX], P4[NX], P5[NX], P6[NX];
     double h = 0.0, dnf = 0.0;
 
+    if (DEFER && mode == MINUTE_IDLE) idid = 1;
+    if (!DEFER || mode != MINUTE_IDLE) {
 #pragma unroll
-    for (int i = 0; i < NX; i++) { yt[i] = y[i]; c.set(H_Y + i, y[i]); }
+        for (int i = 0; i < NX; i++) { yt[i] = y[i]; c.set(H_Y + i, y[i]); }
+    }
+    if (DEFER && mode == MINUTE_RESUME) {
+        h = sp->h; x = sp->x; facold = sp->facold;
+        nstep = sp->nstep; naccpt = sp->naccpt; cnt.nrej = sp->nrej; reject = sp->reject != 0;
+        phase = PH_RESUME;
+    }
 
     // The loop condition is a warp vote: lanes whose minute is complete wait here instead of running ahead
     // into the next minute on their own (without it ptxas leaves the warp split for the rest of the episode:
@@ -382,6 +406,11 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
             begin_step = true;
         } break;
+        case PH_RESUME:                                      // (the RHS of this pass is not used) k1 comes back from H_K1
+#pragma unroll
+            for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
+            begin_step = true;
+            break;
         case PH_S2:                                          // kt = k2; the sums start here from k1 (shared memory)
 #pragma unroll
             for (int i = 0; i < NX; i++) {
@@ -471,7 +500,14 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         } break;
         }
         if (begin_step) {                                    // kt = k1 of the step that starts here
-            if (nstep > NMAX) idid = -2;
+            if (DEFER && cap > 0 && nstep >= cap) {          // put the rest of this minute aside
+#pragma unroll
+                for (int i = 0; i < NX; i++) c.set(H_K1 + i, kt[i]);
+                sp->h = h; sp->x = x; sp->facold = facold;
+                sp->nstep = nstep; sp->naccpt = naccpt; sp->nrej = cnt.nrej; sp->reject = reject ? 1 : 0;
+                idid = IDID_SUSPENDED;
+            }
+            else if (nstep > NMAX) idid = -2;
             else if (0.1 * fabs(h) <= fabs(x) * UROUND) idid = -3;
             else {
                 if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
@@ -487,8 +523,10 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             }
         }
     }
+    if (DEFER && mode == MINUTE_IDLE) return 1;
 #pragma unroll
     for (int i = 0; i < NX; i++) y[i] = c(H_Y + i);
+    if (DEFER && idid == IDID_SUSPENDED) return idid;
     if (carry_h) h_carry = h;
     cnt.nstep += nstep;
     return idid;

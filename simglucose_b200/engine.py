@@ -143,6 +143,12 @@ class BatchEngine:
         _capi.check(self.lib.sg_patient_step(self._h, _ptr(c), _ptr(i), _ptr(out), _stream_ptr()))
         return out
 
+    def set_step_cap(self, cap):
+        """Heavy-minute compaction (sg_set_step_cap): minutes needing more than `cap` DOPRI5 steps are finished by a
+        second launch over the compacted list.  For populations with independent meal schedules; 0 = off."""
+        _capi.check(self.lib.sg_set_step_cap(self._h, int(cap)))
+        self.step_cap = int(cap)
+
     def set_t0(self, t0):
         """patient.t at the next reset (T1DPatient(t0=...), t1dpatient.py:27,277)."""
         _capi.check(self.lib.sg_set_t0(self._h, int(t0)))

@@ -28,15 +28,20 @@ _T = {name: i for i, name in enumerate(_capi.TRACE_COLS)}
 class T1DSimVecEnv(object):
     def __init__(self, num_envs, patient_names=None, seed=0, start_hour=0, horizon_steps=480, sensor='Dexcom',
                  pump='Insulet', stream_mode='device', group_size=1, params=None, x0=None, auto_reset=False,
-                 device=0, carry_h=False, fma=False, episode_offset=0):
+                 device=0, carry_h=False, fma=False, episode_offset=0, step_cap=None):
         """patient_names: list of names / 1-based ids cycled over the environments (default: the 30 virtual
         patients in table order).  params [32, E] / x0 [13, E]: per-environment overrides (perturbed
         populations).  group_size: environments per shared stream (the reference shares RandomScenario(seed)
-        and CGMSensor(seed) across the patients of one batch_sim)."""
+        and CGMSensor(seed) across the patients of one batch_sim).  step_cap: heavy-minute compaction
+        (BatchEngine.set_step_cap) for step(); default 5 when every environment has a meal schedule of its own
+        (group_size == 1) and the population is large enough for the second launch to pay (>= 524,288), else off."""
         self.num_envs = int(num_envs)
         self.engine = BatchEngine(self.num_envs, device=device, carry_h=carry_h, fma=fma, sensor=sensor, pump=pump)
         self.device = self.engine.device
         self.sample_time = self.engine.sample_time
+        auto = 5 if (int(group_size) == 1 and self.num_envs >= 524288) else 0
+        self.step_cap = auto if step_cap is None else int(step_cap)
+        self.engine.set_step_cap(self.step_cap)
         names = P.patient_names() if patient_names is None else list(patient_names)
         rows = np.array([P.patient_row(n) for n in names], dtype=np.int32)
         self.patient_row = torch.from_numpy(rows[np.arange(self.num_envs) % len(rows)]).to(self.device)
@@ -127,8 +132,14 @@ class T1DSimVecEnv(object):
         if controller == 'bb' and ctrl is None and ctrl_rows is None:
             q = torch.from_numpy(P.quest_table()).to(self.device)[self.patient_row.long()]
             ctrl_rows = torch.stack([torch.full_like(q[:, 0], 140.0), q[:, 0], q[:, 1], torch.zeros_like(q[:, 0])])
-        out = self.engine.run(n_steps, controller=controller, ctrl=ctrl, ctrl_rows=ctrl_rows, actions=actions,
-                              trace=trace)
+        if self.step_cap:
+            self.engine.set_step_cap(0)                  # one fused launch; the cap is for lockstep stepping
+        try:
+            out = self.engine.run(n_steps, controller=controller, ctrl=ctrl, ctrl_rows=ctrl_rows, actions=actions,
+                                  trace=trace)
+        finally:
+            if self.step_cap:
+                self.engine.set_step_cap(self.step_cap)
         self.steps += n_steps
         return out
 

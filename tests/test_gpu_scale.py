@@ -130,3 +130,50 @@ def test_config3_size_perturbed_population():
         assert np.array_equal(st[[0, 8, 9, 10, 11, 12, 13, 14, 15], j], ref[[0, 8, 9, 10, 11, 12, 13, 14, 15]])
         assert abs(st[1, j] - ref[1]) <= 1e-6 * abs(ref[1])
     eng.close()
+
+
+@pytest.mark.parametrize('controller', ['bb', 'actions'])
+def test_step_cap_compaction_is_bit_identical(controller):
+    """sg_set_step_cap: heavy minutes finished by the second launch give the same bits as the single kernel
+    (trace, per-minute DOPRI5 counters, state, statistics), fused and lockstep, independent schedules per lane."""
+    import torch
+    from simglucose_b200 import params as P, streams as S
+    from simglucose_b200.engine import BatchEngine
+    E, n_steps = 20000, 200                               # 10 h from 06:00: breakfast and lunch onsets
+    dev = torch.device('cuda', 0)
+    rows = (torch.arange(E, device=dev, dtype=torch.int64) % 30).to(torch.int32)
+    noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=9, group_size=1, device=dev)
+    mm, mg = S.device_scenarios(E, n_steps * 3, start_minute=360, seed=9, group_size=1, device=dev)
+    q = torch.from_numpy(P.quest_table()).cuda()[rows.long()]
+    ctrl_rows = torch.stack([torch.full_like(q[:, 0], 140.0), q[:, 0], q[:, 1], torch.zeros_like(q[:, 0])]).contiguous()
+    acts = None
+    if controller == 'actions':
+        acts = torch.stack([S.device_uniform(2 * E, 0.0, 0.04, seed=1, offset=k * 2 * E).reshape(2, E) for k in range(n_steps)])
+        acts[:, 1] = torch.where(acts[:, 1] > 0.039, acts[:, 1] * 20, torch.zeros_like(acts[:, 1]))    # occasional boluses
+
+    def run(cap, lockstep=False):
+        eng = BatchEngine(E)
+        eng.set_step_cap(cap)
+        eng.reset(rows, noise, mm, mg, row0=False)
+        if lockstep:
+            tr = torch.stack([eng.step(acts[k, 0], acts[k, 1]).clone() for k in range(n_steps)])
+            cn = None
+        else:
+            out = eng.run(n_steps, controller=controller, ctrl_rows=ctrl_rows if controller == 'bb' else None,
+                          actions=acts, trace=True, counters=True)
+            tr, cn = out['trace'], out['counters']
+        res = (tr, cn, eng.state(), eng.stats(), eng.status(), eng.launches)
+        eng.close()
+        return res
+    base = run(0)
+    capped = run(5)
+    assert torch.equal(base[0], capped[0], ) or torch.equal(torch.nan_to_num(base[0]), torch.nan_to_num(capped[0]))
+    assert torch.equal(base[1], capped[1]) and torch.equal(base[2], capped[2])
+    assert torch.equal(base[3], capped[3]) and torch.equal(base[4], capped[4])
+    assert capped[5] == 1 + 2 * n_steps and base[5] == 2                     # reset + (A, B) per env-step
+    heavy = int((base[1][:, 0, :] > 5).sum())
+    assert heavy > 100                                                        # the cap was exercised
+    if controller == 'actions':
+        lock = run(6, lockstep=True)
+        assert torch.equal(torch.nan_to_num(lock[0]), torch.nan_to_num(base[0]))
+        assert torch.equal(lock[2], base[2]) and torch.equal(lock[3], base[3])

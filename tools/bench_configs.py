@@ -62,12 +62,12 @@ def config2(scale):
     agg = summarize(env.statistics())
     env.close()
     return {'config': 'configs[2] lockstep vector env, %d episodes x %d env-steps, basal ~ U(0, 0.05) U/min on device, '
-                      'risk_diff reward, no auto-reset' % (E, n_steps),
+                      'risk_diff reward, no auto-reset, step_cap %d' % (E, n_steps, env.step_cap),
             'value': E * n_steps * 3 / sec, 'unit': 'patient-sim-minutes/sec', 'seconds': sec, 'env_steps_per_s': E * n_steps / sec,
             'gpu_launches': int(launches), 'ms_per_env_step': 1e3 * sec / n_steps, 'population': agg}
 
 
-def config3(scale):
+def config3(scale, cap=0):
     E, days = int(262144 * scale) // 64 * 64, 7
     n_steps = days * 480
     dev = torch.device('cuda', 0)
@@ -78,6 +78,7 @@ def config3(scale):
     noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=1234, group_size=1, device=dev)
     mm, mg = S.device_scenarios(E, n_steps * 3, start_minute=0, seed=1234, group_size=1, device=dev)
     eng = BatchEngine(E)
+    eng.set_step_cap(cap)
 
     def run():
         eng.reset(rows, noise, mm, mg, params=params, row0=False)
@@ -88,9 +89,9 @@ def config3(scale):
     failed = int((eng.status() < 0).sum().item())
     eng.close()
     return {'config': 'configs[3] perturbed population (+-10 %% per parameter, Philox seed 1234), %d episodes x %d days, '
-                      'BBController, independent scenario / sensor streams per episode (one shard chunk)' % (E, days),
-            'value': E * n_steps * 3 / sec, 'unit': 'patient-sim-minutes/sec', 'seconds': sec, 'gpu_launches': 4,
-            'solver_failures': failed, 'population': agg}
+                      'BBController, independent scenario / sensor streams per episode (one shard chunk), step_cap %d' % (E, days, cap),
+            'value': E * n_steps * 3 / sec, 'unit': 'patient-sim-minutes/sec', 'seconds': sec,
+            'gpu_launches': 4 if cap == 0 else 3 + 2 * n_steps, 'solver_failures': failed, 'population': agg}
 
 
 def config4(scale):
