@@ -212,7 +212,7 @@ assert agg[0] == 10.0 * n_total and agg[2] == 0 and agg[3] == 200 and agg[13] ==
 assert abs(agg[1] - (100 * n_total + n_total * (n_total - 1) / 2)) < 1e-9
 assert abs(s['pct_in_range'] - 70.0) < 1e-12 and s['episodes_done'] == 51
 dist.destroy_process_group()
-print('rank', rank, 'ok')
+sys.stdout.write('rank %%d ok\n' %% rank)        # one write() per rank so the lines cannot interleave
 '''
 
 
