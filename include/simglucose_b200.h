@@ -44,6 +44,10 @@ typedef enum { SG_OK = 0, SG_ERR_ARG = -1, SG_ERR_CUDA = -2, SG_ERR_STATE = -3, 
 #define SG_FLAG_CARRY_H 1u   /* scipy 1.6.3 (Pipfile.lock) behaviour: the step size proposed at the end of one
                                 minute starts the next (WORK(7)=H); default 0 = scipy >= 1.7: HINIT every minute */
 #define SG_FLAG_FMA     2u   /* allow FMA contraction in the kernels (faster; not decision-identical to scipy) */
+#define SG_FLAG_PAIR    4u   /* sg_run / sg_step launch the warp-pair kernel: two threads (glucose side, insulin
+                                side) per episode.  Same arithmetic per state, bit-identical results in strict
+                                mode; ignored while sg_set_step_cap is active.  The environment variable
+                                SG_PAIR=0/1 overrides the flag at sg_create (A/B measurements). */
 
 /* Controller fused into sg_run. */
 typedef enum {

@@ -4,6 +4,7 @@
 #include "sg_kernels.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -109,6 +110,7 @@ int sg_create(int device, int64_t capacity, uint32_t flags, sg_handle *out)
     if (!g.ok) return fail(SG_ERR_CUDA, "sg_create: cudaSetDevice failed");
     sg_context *h = new (std::nothrow) sg_context();
     if (!h) return fail(SG_ERR_NOMEM, "sg_create: host allocation failed");
+    if (const char *ev = getenv("SG_PAIR")) flags = (ev[0] == '1') ? (flags | SG_FLAG_PAIR) : (flags & ~SG_FLAG_PAIR);
     h->device = device; h->cap = capacity; h->flags = flags;
     h->max_partials = sg_strict::reduce_blocks(capacity);
     ce = cudaMalloc(&h->sd, sizeof(double) * sgk::SD_COUNT * capacity);
@@ -222,8 +224,11 @@ static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, co
         h->steps_done += n_steps;
         return SG_OK;
     }
-    cudaError_t ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream)
-                                : sg_strict::launch_run(a, (cudaStream_t)stream);
+    cudaError_t ce;
+    if (h->flags & SG_FLAG_PAIR)
+        ce = use_fma(h) ? sg_fma::launch_run_pair(a, (cudaStream_t)stream) : sg_strict::launch_run_pair(a, (cudaStream_t)stream);
+    else
+        ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream) : sg_strict::launch_run(a, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
     h->launches++;
     h->steps_done += n_steps;

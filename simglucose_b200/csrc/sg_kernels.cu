@@ -606,6 +606,8 @@ cudaError_t launch_run_capped(const EpisodeArgs &a, cudaStream_t s)
     return cudaGetLastError();
 }
 
+#include "sg_pair.cuh"
+
 cudaError_t launch_patient_step(const PatientArgs &a, cudaStream_t s)
 {
     constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);

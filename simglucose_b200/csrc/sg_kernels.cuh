@@ -129,6 +129,7 @@ struct ReduceArgs {
     cudaError_t launch_reset(const sgk::EpisodeArgs &a, cudaStream_t s);      \
     cudaError_t launch_run(const sgk::EpisodeArgs &a, cudaStream_t s);        \
     cudaError_t launch_run_capped(const sgk::EpisodeArgs &a, cudaStream_t s); \
+    cudaError_t launch_run_pair(const sgk::EpisodeArgs &a, cudaStream_t s);   \
     cudaError_t launch_reduce(const sgk::ReduceArgs &a, cudaStream_t s);      \
     cudaError_t launch_patient_step(const sgk::PatientArgs &a, cudaStream_t s); \
     cudaError_t launch_model(const sgk::ModelArgs &a, cudaStream_t s);        \
