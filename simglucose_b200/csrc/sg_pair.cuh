@@ -2,43 +2,49 @@
 //
 // 64-thread blocks own 32 patient-episodes: lane l of warp 0 (role G) and lane l of warp 1 (role I) work on
 // the SAME episode.  The UVa/Padova model splits along its physiology (t1dpatient.py:118-208):
-//   role G  states x0..x4   gut (with the tanh gastric emptying) and glucose kinetics; reads x6, x8 of role I
-//   role I  states x5..x12  insulin kinetics / action, s.c. insulin and s.c. glucose; reads x3 of role G
-// so each RHS pass needs three doubles to cross between the warps (a double-buffered mailbox in shared memory and
-// one __syncthreads per pass).  The error / HINIT norms are sums over the 13 states in index order: G adds its
-// five terms, I continues with its eight, runs the step-size controller and publishes the decision (a code word
-// and h); G only follows.  Role I also owns the closed loop around the integrator (sensor, controller, pump, risk,
-// statistics), role G the meal state machine.  Every state is integrated by exactly one thread with the operation
-// order of the single-thread kernel, so in strict arithmetic the results are bit-identical to run_kernel.
-//
-// Why: run_kernel needs 248 registers per thread -> two warps per scheduler, 4.9 cycles of latency per issued
-// instruction and nothing to cover it (profiles/r01_s25_*).  Each role fits in 128 registers -> 16 warps per SM
-// on the same 256 resident episodes, and the per-pass dependency chains are half as long.
+//   role G  x0..x4, x12   gut (with the tanh gastric emptying), glucose kinetics, s.c. glucose; reads x6, x8
+//   role I  x5..x11       insulin kinetics / action and s.c. insulin; reads nothing of role G
+// Both roles run the SAME instruction stream over seven state slots (role G pads one): only the RHS halves and
+// the step-size control branch on the role.  That matters: the first version of this kernel gave each role a
+// loop body of its own, 32 KB of hot code together, and lost 27 % to instruction fetch (profiles/r01_s30_*).
+// Per RHS pass two doubles cross from I to G through a double-buffered mailbox in shared memory, one
+// __syncthreads per pass.  The error / HINIT norms are sums over the 13 states in index order: role I reads the
+// terms of role G from shared memory, adds everything in that order, runs the step-size controller and
+// publishes the decision (a code word and h); G only follows.  Role I also owns the closed loop around the
+// integrator (sensor, controller, pump, risk, statistics), role G the meal state machine.  Every state is
+// integrated by exactly one thread with the operation order of the single-thread kernel, so in strict
+// arithmetic the results are bit-identical to run_kernel (tests/test_gpu_pair.py).
 
 namespace pair {
 
 constexpr int PL = 32;                   // episodes per block
 constexpr int PBLOCK = 64;               // threads per block: warp 0 = role G, warp 1 = role I
-constexpr int NG = 5, NI = 8;            // states per role
+constexpr int NS = 7;                    // state slots per role
 using Col = Column<PL>;
 
-enum MailRow {
-    M_X3A = H_COUNT, M_X6A, M_X8A,       // trial-state values that cross between the roles, buffer 0
-    M_X3B, M_X6B, M_X8B,                 //                                                  buffer 1
-    M_S0, M_S1,                          // partial norms of role G
+// Rows of the episode's shared-memory column after the parameter rows (H_K1 is the first vector row of the
+// single-thread layout).  Vector rows: [role][slot]; role G slots = x0, x1, x2, x3, x4, x12, pad; role I = x5..x11.
+enum PairRow {
+    R_K1 = H_K1, R_P7 = R_K1 + 2 * NS, R_PE = R_P7 + 2 * NS, R_Y = R_PE + 2 * NS,
+    M_X6A = R_Y + 2 * NS, M_X8A,         // trial-state values role G reads, buffer 0
+    M_X6B, M_X8B,                        //                                  buffer 1
     M_H, M_ACT,                          // decision of role I
     M_CHOA, M_CHOB,                      // running mean of the announced grams over the env-step (role G -> role I,
                                          // info['meal']), double-buffered by minute parity
-    M_BG, M_CGM, M_LAST_CGM, M_HCARRY,   // role I: env-step accumulators and per-minute state parked outside registers
+    M_LAST_CGM,                          // CGMSensor._last_CGM (role I)
     PAIR_ROWS
 };
+
+// state index (t1dpatient.py order) -> row offset inside a vector
+__device__ __forceinline__ int state_row(int i) { return i < 5 ? i : (i < 12 ? i + 2 : 5); }
 
 enum ActBits { ACT_COMMIT = 1, ACT_BEGIN = 2, ACT_K1SMEM = 4, ACT_PROBE = 8, ACT_STOP = 16 };
 enum Phase { PH_K1 = 0, PH_HINIT, PH_S2, PH_S3, PH_S4, PH_S5, PH_S6, PH_S7 };
 
 // ---- the two halves of T1DPatient.model ---------------------------------------------------------------------
-__device__ __forceinline__ void rhs_g(const Col &c, double d, bool fed, const double (&x)[NG], double x6, double x8,
-                                      double (&dx)[NG])
+// slots: x0, x1, x2, x3, x4, x12, pad
+__device__ __forceinline__ void rhs_g(const Col &c, double d, bool fed, const double (&x)[NS], double x6, double x8,
+                                      double (&dx)[NS])
 {
     const double kmax = c(H_kmax);
     const double qsto = x[0] + x[1];                                        // :126
@@ -63,10 +69,13 @@ __device__ __forceinline__ void rhs_g(const Col &c, double d, bool fed, const do
     const double Vmt = c(H_Vm0) + c(H_Vmx) * x6;                            // :169
     const double Uidt = sgm::div_nr(Vmt * x[4], c(H_Km0) + x[4]);           // :171
     dx[4] = mask_nonneg(x[4], -Uidt + k1 * x[3] - k2 * x[4]);               // :172-173
+    const double ksc = c(H_ksc);
+    dx[5] = mask_nonneg(x[5], -ksc * x[5] + ksc * x[3]);                    // :201-202
+    dx[6] = 0.0;
 }
 
-// x[i] is state 5 + i
-__device__ __forceinline__ void rhs_i(const Col &c, double ins, const double (&x)[NI], double x3, double (&dx)[NI])
+// slots: x5, x6, x7, x8, x9, x10, x11
+__device__ __forceinline__ void rhs_i(const Col &c, double ins, const double (&x)[NS], double (&dx)[NS])
 {
     const double ka2 = c(H_ka2), m2 = c(H_m2);
     dx[0] = mask_nonneg(x[0], -c(H_m24) * x[0] + c(H_m1) * x[4] + c(H_ka1) * x[5] + ka2 * x[6]);   // :176-179
@@ -79,20 +88,44 @@ __device__ __forceinline__ void rhs_i(const Col &c, double ins, const double (&x
     const double kd = c(H_kd);
     dx[5] = mask_nonneg(x[5], ins - c(H_kad) * x[5]);                       // :194-195
     dx[6] = mask_nonneg(x[6], kd * x[5] - ka2 * x[6]);                      // :197-198
-    const double ksc = c(H_ksc);
-    dx[7] = mask_nonneg(x[7], -ksc * x[7] + ksc * x3);                      // :201-202
 }
 
-// ---- once-per-minute / once-per-step scalar pieces of role I (kept out of the loop body) -------------------
-static __device__ __noinline__ double hinit_first_finish(double dnf, double dny, double hmax)
+// ---- once-per-minute / once-per-step pieces of role I (not inlined: the loop body has to stay small) --------
+struct HinitGuess2 { double h, dnf; };
+
+// HINIT, first half, over all 13 states in index order (rows of both roles): h = 0.01 * |y| / |k1|.
+static __device__ __noinline__ HinitGuess2 hinit_first_all(double *col, double hmax)
 {
+    const Col c{col};
+    double dny = 0.0, dnf = 0.0;
+#pragma unroll 1
+    for (int i = 0; i < NX; i++) {
+        const int r_ = state_row(i);
+        const double yi = c(R_Y + r_);
+        const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
+        const double sk = ATOL + RTOL * fabs(yi);
+        const double a = sgm::div_r(c(R_K1 + r_), sk, r), b = sgm::div_r(yi, sk, r);
+        dnf = dnf + a * a;
+        dny = dny + b * b;
+    }
     double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
-    return fmin(h, hmax);
+    h = fmin(h, hmax);
+    return HinitGuess2{h, dnf};
 }
 
-static __device__ __noinline__ double hinit_second_finish(double der2sum, double dnf, double h, double hmax)
+// HINIT, second half: second-derivative estimate from f(x + h, y + h*k1) (R_P7 rows) and k1 (R_K1 rows).
+static __device__ __noinline__ double hinit_second_all(double *col, double h, double dnf, double hmax)
 {
-    const double der2 = sqrt(der2sum) / h;
+    const Col c{col};
+    double der2 = 0.0;
+#pragma unroll 1
+    for (int i = 0; i < NX; i++) {
+        const int r_ = state_row(i);
+        const double sk = ATOL + RTOL * fabs(c(R_Y + r_));
+        const double a = sgm::div_nr(c(R_P7 + r_) - c(R_K1 + r_), sk);
+        der2 = der2 + a * a;
+    }
+    der2 = sqrt(der2) / h;
     const double der12 = fmax(fabs(der2), sqrt(dnf));
     const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
     return fmin(fmin(100.0 * fabs(h), h1), hmax);
@@ -100,14 +133,14 @@ static __device__ __noinline__ double hinit_second_finish(double der2sum, double
 
 // Integrator control state of role I.
 struct Ctl {
-    double x, xend, facold;
+    double x, xend, facold, dnf;
     int nstep, naccpt, nrej, idid;
     bool last, reject;
 };
 // hmax = |xend - x0| of one integrate(t + 1) call: exactly 1.0 for integer minutes below 2^52
 constexpr double HMAX = 1.0;
 
-// Start a step of size h at c.x (DOPCOR's loop head): returns the action bits, h may be shortened to hit xend.
+// Start a step of size h at s.x (DOPCOR's loop head): returns the action bits, h may be shortened to hit xend.
 __device__ __forceinline__ int begin_step(Ctl &s, double &h)
 {
     if (s.nstep > NMAX) { s.idid = -2; return ACT_STOP; }
@@ -117,28 +150,62 @@ __device__ __forceinline__ int begin_step(Ctl &s, double &h)
     return ACT_BEGIN;
 }
 
-// One call of ode('dopri5').integrate(t + 1) by the warp pair.  The accepted state stays in the H_Y rows of the
-// episode's column between calls (this role's states are rows OFF .. OFF+N-1).
+// Error estimate of a finished step -> accept / reject, next step size (DOPCOR).  Returns the action bits.
+__device__ __forceinline__ int control_step(Ctl &s, double errsum, double &h)
+{
+    const StepControl sc = step_control(errsum, s.facold, h);
+    const double err = sc.err;
+    double hnew = sc.hnew_accept;
+    bool begin = false;
+    int code;
+    if (err <= 1.0) {
+        s.facold = sgm::max_sel(err, 1.0e-4);
+        s.naccpt++;
+        code = ACT_COMMIT;                                   // kt is k1 of the next step (FSAL)
+        s.x = s.x + h;
+        if (s.last) {
+            s.idid = 1;
+            code |= ACT_STOP;
+        } else {
+            if (fabs(hnew) > HMAX) hnew = HMAX;
+            if (s.reject) hnew = sgm::min_sel(fabs(hnew), fabs(h));
+            s.reject = false;
+            begin = true;
+        }
+    } else {
+        hnew = sc.hnew_reject;
+        s.reject = true;
+        if (s.naccpt >= 1) s.nrej++;
+        s.last = false;
+        code = ACT_K1SMEM;
+        begin = true;
+    }
+    h = hnew;
+    if (begin) code |= begin_step(s, h);
+    return code;
+}
+
+// One call of ode('dopri5').integrate(t + 1) by the warp pair.  The accepted state stays in the R_Y rows of the
+// episode's column between calls.  c: the episode's column; v: the same column shifted to this role's vector rows.
 // u: CHO rate * 1000 (role G) / insulin rate per kg (role I).  par: mailbox buffer parity (kept across calls).
-template <int ROLE>
-__device__ __forceinline__ int minute_pair(const Col &c, bool valid, double u, bool fed, double t0, bool carry_h,
+// hc: the episode's WORK(7) slot in the resident state (read / written by role I with SG_FLAG_CARRY_H only).
+__device__ __forceinline__ int minute_pair(const Col &c, const Col &v, const int role, const bool valid, const double u,
+                                           const bool fed, const double t0, const bool carry_h, double *hc,
                                            StepCount &cnt, int &par)
 {
-    constexpr int OFF = ROLE == 0 ? 0 : NG, N = ROLE == 0 ? NG : NI;
     constexpr unsigned FULL = 0xffffffffu;
-    // The stage-4 sum lives only from stage 2 to stage 3: it waits in the H_PE rows, which are first written at
+    // The stage-4 sum lives only from stage 2 to stage 3: it waits in the R_PE rows, which are first written at
     // stage 3.  P5 is dead from stage 5 on: the squared error terms of stage 7 reuse its registers (sq).
-    double yt[N], kt[N], P5[N], P6[N];
-    double (&sq)[N] = P5;
+    double yt[NS], kt[NS], P5[NS], P6[NS];
+    double (&sq)[NS] = P5;
     double h = 0.0;
     int idid = valid ? 0 : 1, phase = PH_K1;
-    Ctl s{t0, t0 + 1.0, 1.0e-4, 0, 0, 0, 0, false, false};
+    Ctl s{t0, t0 + 1.0, 1.0e-4, 0.0, 0, 0, 0, 0, false, false};
 
     if (valid) {
 #pragma unroll
-        for (int i = 0; i < N; i++) yt[i] = c(H_Y + OFF + i);
-        if (ROLE == 0) c.set(M_X3A + 3 * par, yt[3]);
-        else { c.set(M_X6A + 3 * par, yt[1]); c.set(M_X8A + 3 * par, yt[3]); }
+        for (int i = 0; i < NS; i++) yt[i] = v(R_Y + i);
+        if (role == 1) { c.set(M_X6A + 2 * par, yt[1]); c.set(M_X8A + 2 * par, yt[3]); }
     }
     __syncthreads();
 
@@ -148,45 +215,24 @@ __device__ __forceinline__ int minute_pair(const Col &c, bool valid, double u, b
         const bool ctl_phase = phase < PH_S2 || phase == PH_S7;
         const bool ctl_pass = __any_sync(FULL, act && ctl_phase);     // the same in both warps of the pair
         if (act) {
-            if constexpr (ROLE == 0) rhs_g(c, u, fed, yt, c(M_X6A + 3 * par), c(M_X8A + 3 * par), kt);
-            else rhs_i(c, u, yt, c(M_X3A + 3 * par), kt);
+            if (role == 0) rhs_g(c, u, fed, yt, c(M_X6A + 2 * par), c(M_X8A + 2 * par), kt);
+            else rhs_i(c, u, yt, kt);
 
             switch (phase) {
             case PH_K1:                                          // kt = k1 = f(x, y)
 #pragma unroll
-                for (int i = 0; i < N; i++) c.set(H_K1 + OFF + i, kt[i]);
-                if (ROLE == 0) {                                 // HINIT norms, terms 0..4
-                    double dnf = 0.0, dny = 0.0;
-#pragma unroll
-                    for (int i = 0; i < N; i++) {
-                        const double yi = c(H_Y + OFF + i);
-                        const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
-                        const double sk = ATOL + RTOL * fabs(yi);
-                        const double a = sgm::div_r(kt[i], sk, r), b = sgm::div_r(yi, sk, r);
-                        dnf = dnf + a * a;
-                        dny = dny + b * b;
-                    }
-                    c.set(M_S0, dnf); c.set(M_S1, dny);
-                }
+                for (int i = 0; i < NS; i++) v.set(R_K1 + i, kt[i]);
                 break;
             case PH_HINIT:                                       // kt = f(x + h, y + h*k1)
-                if (ROLE == 0) {
-                    double der2 = 0.0;
 #pragma unroll
-                    for (int i = 0; i < N; i++) {
-                        const double sk = ATOL + RTOL * fabs(c(H_Y + OFF + i));
-                        const double a = sgm::div_nr(kt[i] - c(H_K1 + OFF + i), sk);
-                        der2 = der2 + a * a;
-                    }
-                    c.set(M_S0, der2);
-                }
+                for (int i = 0; i < NS; i++) v.set(R_P7 + i, kt[i]);
                 break;
             case PH_S2:                                          // kt = k2
 #pragma unroll
-                for (int i = 0; i < N; i++) {
-                    const double k1 = c(H_K1 + OFF + i);
-                    yt[i] = c(H_Y + OFF + i) + h * (A31 * k1 + A32 * kt[i]);
-                    c.set(H_PE + OFF + i, A41 * k1 + A42 * kt[i]);
+                for (int i = 0; i < NS; i++) {
+                    const double k1 = v(R_K1 + i);
+                    yt[i] = v(R_Y + i) + h * (A31 * k1 + A32 * kt[i]);
+                    v.set(R_PE + i, A41 * k1 + A42 * kt[i]);
                     P5[i] = A51 * k1 + A52 * kt[i];
                     P6[i] = A61 * k1 + A62 * kt[i];
                 }
@@ -194,267 +240,168 @@ __device__ __forceinline__ int minute_pair(const Col &c, bool valid, double u, b
                 break;
             case PH_S3:                                          // kt = k3
 #pragma unroll
-                for (int i = 0; i < N; i++) {
-                    const double k1 = c(H_K1 + OFF + i);
-                    yt[i] = c(H_Y + OFF + i) + h * (c(H_PE + OFF + i) + A43 * kt[i]);
+                for (int i = 0; i < NS; i++) {
+                    const double k1 = v(R_K1 + i);
+                    yt[i] = v(R_Y + i) + h * (v(R_PE + i) + A43 * kt[i]);
                     P5[i] = P5[i] + A53 * kt[i];
                     P6[i] = P6[i] + A63 * kt[i];
-                    c.set(H_P7 + OFF + i, A71 * k1 + A73 * kt[i]);
-                    c.set(H_PE + OFF + i, E1 * k1 + E3 * kt[i]);
+                    v.set(R_P7 + i, A71 * k1 + A73 * kt[i]);
+                    v.set(R_PE + i, E1 * k1 + E3 * kt[i]);
                 }
                 phase = PH_S4;
                 break;
             case PH_S4:                                          // kt = k4
 #pragma unroll
-                for (int i = 0; i < N; i++) {
-                    yt[i] = c(H_Y + OFF + i) + h * (P5[i] + A54 * kt[i]);
+                for (int i = 0; i < NS; i++) {
+                    yt[i] = v(R_Y + i) + h * (P5[i] + A54 * kt[i]);
                     P6[i] = P6[i] + A64 * kt[i];
-                    c.set(H_P7 + OFF + i, c(H_P7 + OFF + i) + A74 * kt[i]);
-                    c.set(H_PE + OFF + i, c(H_PE + OFF + i) + E4 * kt[i]);
+                    v.set(R_P7 + i, v(R_P7 + i) + A74 * kt[i]);
+                    v.set(R_PE + i, v(R_PE + i) + E4 * kt[i]);
                 }
                 phase = PH_S5;
                 break;
             case PH_S5:                                          // kt = k5
 #pragma unroll
-                for (int i = 0; i < N; i++) {
-                    yt[i] = c(H_Y + OFF + i) + h * (P6[i] + A65 * kt[i]);
-                    c.set(H_P7 + OFF + i, c(H_P7 + OFF + i) + A75 * kt[i]);
-                    c.set(H_PE + OFF + i, c(H_PE + OFF + i) + E5 * kt[i]);
+                for (int i = 0; i < NS; i++) {
+                    yt[i] = v(R_Y + i) + h * (P6[i] + A65 * kt[i]);
+                    v.set(R_P7 + i, v(R_P7 + i) + A75 * kt[i]);
+                    v.set(R_PE + i, v(R_PE + i) + E5 * kt[i]);
                 }
                 phase = PH_S6;
                 break;
             case PH_S6:                                          // kt = k6; yt becomes the 5th-order solution
 #pragma unroll
-                for (int i = 0; i < N; i++) {
-                    yt[i] = c(H_Y + OFF + i) + h * (c(H_P7 + OFF + i) + A76 * kt[i]);
-                    c.set(H_PE + OFF + i, c(H_PE + OFF + i) + E6 * kt[i]);
+                for (int i = 0; i < NS; i++) {
+                    yt[i] = v(R_Y + i) + h * (v(R_P7 + i) + A76 * kt[i]);
+                    v.set(R_PE + i, v(R_PE + i) + E6 * kt[i]);
                 }
                 phase = PH_S7;
                 break;
-            default: {                                           // kt = k7: squared scaled error terms
+            default:                                             // kt = k7: squared scaled error terms
 #pragma unroll
-                for (int i = 0; i < N; i++) {
-                    const double e = (c(H_PE + OFF + i) + E7 * kt[i]) * h;
-                    const double sk = ATOL + RTOL * sgm::max_sel(fabs(c(H_Y + OFF + i)), fabs(yt[i]));
+                for (int i = 0; i < NS; i++) {
+                    const double e = (v(R_PE + i) + E7 * kt[i]) * h;
+                    const double sk = ATOL + RTOL * sgm::max_sel(fabs(v(R_Y + i)), fabs(yt[i]));
                     const double a = sgm::div_nr(e, sk);
                     sq[i] = a * a;
+                    v.set(R_PE + i, sq[i]);                      // role I reads the terms of role G from here
                 }
-                if (ROLE == 0) {
-                    double err = 0.0;
-#pragma unroll
-                    for (int i = 0; i < N; i++) err = err + sq[i];
-                    c.set(M_S0, err);
-                }
-            } break;
+                break;
             }
         }
 
         if (ctl_pass) {
-            __syncthreads();                                     // partial norms of role G are visible
+            __syncthreads();                                     // the rows written by role G are visible
             int code = 0;
-            if (ROLE == 1 && act && ctl_phase) {
+            if (role == 1 && act && ctl_phase) {
                 if (phase == PH_K1) {
-                    h = carry_h ? c(M_HCARRY) : 0.0;
+                    h = carry_h ? *hc : 0.0;
                     if (h == 0.0) {                              // HINIT, first half
-                        double dnf = c(M_S0), dny = c(M_S1);
-#pragma unroll
-                        for (int i = 0; i < N; i++) {
-                            const double yi = c(H_Y + OFF + i);
-                            const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
-                            const double sk = ATOL + RTOL * fabs(yi);
-                            const double a = sgm::div_r(kt[i], sk, r), b = sgm::div_r(yi, sk, r);
-                            dnf = dnf + a * a;
-                            dny = dny + b * b;
-                        }
-                        h = hinit_first_finish(dnf, dny, HMAX);
-                        c.set(M_S1, dnf);                        // needed again by the second half (next pass)
+                        const HinitGuess2 g = hinit_first_all(c.base, HMAX);
+                        h = g.h;
+                        s.dnf = g.dnf;
                         code = ACT_PROBE;
                     } else {
                         code = begin_step(s, h);
                     }
                 } else if (phase == PH_HINIT) {                  // HINIT, second half
-                    double der2 = c(M_S0);
-#pragma unroll
-                    for (int i = 0; i < N; i++) {
-                        const double sk = ATOL + RTOL * fabs(c(H_Y + OFF + i));
-                        const double a = sgm::div_nr(kt[i] - c(H_K1 + OFF + i), sk);
-                        der2 = der2 + a * a;
-                    }
-                    h = hinit_second_finish(der2, c(M_S1), h, HMAX);
+                    h = hinit_second_all(c.base, h, s.dnf, HMAX);
                     code = ACT_K1SMEM | begin_step(s, h);
-                } else {                                         // error estimate + step-size control
-                    double err = c(M_S0);
+                } else {                                         // error norm in state order: x0..x4, x5..x11, x12
+                    double err = 0.0;
 #pragma unroll
-                    for (int i = 0; i < N; i++) err = err + sq[i];
-                    const StepControl sc = step_control(err, s.facold, h);
-                    err = sc.err;
-                    double hnew = sc.hnew_accept;
-                    bool begin = false;
-                    if (err <= 1.0) {
-                        s.facold = sgm::max_sel(err, 1.0e-4);
-                        s.naccpt++;
-                        code = ACT_COMMIT;                       // kt is k1 of the next step (FSAL)
-                        s.x = s.x + h;
-                        if (s.last) {
-                            s.idid = 1;
-                            code |= ACT_STOP;
-                        } else {
-                            if (fabs(hnew) > HMAX) hnew = HMAX;
-                            if (s.reject) hnew = sgm::min_sel(fabs(hnew), fabs(h));
-                            s.reject = false;
-                            begin = true;
-                        }
-                    } else {
-                        hnew = sc.hnew_reject;
-                        s.reject = true;
-                        if (s.naccpt >= 1) s.nrej++;
-                        s.last = false;
-                        code = ACT_K1SMEM;
-                        begin = true;
-                    }
-                    h = hnew;
-                    if (begin) code |= begin_step(s, h);
+                    for (int i = 0; i < 5; i++) err = err + c(R_PE + i);
+#pragma unroll
+                    for (int i = 0; i < NS; i++) err = err + sq[i];
+                    err = err + c(R_PE + 5);
+                    code = control_step(s, err, h);
                 }
                 c.set(M_H, h);
                 c.set(M_ACT, (double)code);
             }
             __syncthreads();                                     // the decision is visible
             if (act && ctl_phase) {
-                if (ROLE == 0) { code = (int)c(M_ACT); h = c(M_H); }
+                if (role == 0) { code = (int)c(M_ACT); h = c(M_H); }
                 if (code & ACT_COMMIT) {
 #pragma unroll
-                    for (int i = 0; i < N; i++) c.set(H_Y + OFF + i, yt[i]);
+                    for (int i = 0; i < NS; i++) v.set(R_Y + i, yt[i]);
                 }
                 if (code & ACT_K1SMEM) {
 #pragma unroll
-                    for (int i = 0; i < N; i++) kt[i] = c(H_K1 + OFF + i);
+                    for (int i = 0; i < NS; i++) kt[i] = v(R_K1 + i);
                 }
                 if (code & ACT_PROBE) {
 #pragma unroll
-                    for (int i = 0; i < N; i++) yt[i] = c(H_Y + OFF + i) + h * kt[i];
+                    for (int i = 0; i < NS; i++) yt[i] = v(R_Y + i) + h * kt[i];
                     phase = PH_HINIT;
                 }
                 if (code & ACT_BEGIN) {                          // kt = k1 of the step that starts here
                     const double ha = h * A21;
                     if (!(code & ACT_K1SMEM)) {
 #pragma unroll
-                        for (int i = 0; i < N; i++) c.set(H_K1 + OFF + i, kt[i]);
+                        for (int i = 0; i < NS; i++) v.set(R_K1 + i, kt[i]);
                     }
 #pragma unroll
-                    for (int i = 0; i < N; i++) yt[i] = c(H_Y + OFF + i) + ha * kt[i];
+                    for (int i = 0; i < NS; i++) yt[i] = v(R_Y + i) + ha * kt[i];
                     phase = PH_S2;
                 }
-                if (code & ACT_STOP) idid = (ROLE == 1) ? s.idid : 1;
+                if (code & ACT_STOP) idid = (role == 1) ? s.idid : 1;
             }
         }
 
         par ^= 1;
-        if (act) {                                               // trial-state values the other role reads next pass
-            if (ROLE == 0) c.set(M_X3A + 3 * par, yt[3]);
-            else { c.set(M_X6A + 3 * par, yt[1]); c.set(M_X8A + 3 * par, yt[3]); }
-        }
+        if (act && role == 1) { c.set(M_X6A + 2 * par, yt[1]); c.set(M_X8A + 2 * par, yt[3]); }
         __syncthreads();
     }
-    if (ROLE == 1) {
-        if (carry_h && valid) c.set(M_HCARRY, h);
+    if (role == 1) {
+        if (carry_h && valid) *hc = h;
         cnt.nstep += s.nstep;
         cnt.nrej += s.nrej;
     }
     return idid;
 }
 
-// ---- role G: meal state machine + gut / glucose kinetics ----------------------------------------------------
-__device__ __forceinline__ void episode_g(const EpisodeArgs &a, const int64_t e, const bool valid, const Col &c)
+// The episode loop of both roles (SimObj.simulate / T1DSimEnv.step, env.py:48-117).  role 0: meal state machine
+// (t1dpatient.py:82-107) and the glucose side of the patient; role 1: sensor, controller, pump, risk, statistics
+// and the insulin side.
+__device__ __forceinline__ void episode_pair(const EpisodeArgs &a, const int64_t e, const bool valid, const int role,
+                                             const Col &c)
 {
+    const Col v{c.base + role * NS * PL};
     double *sd = a.sd + e;
     int32_t *si = a.si + e;
     Meal meal{0.0, 0.0, 0.0, 0.0, 0};
-    int minute = 0, meal_pos = 0, next_mm = -1;
+    int minute = 0, meal_pos = 0, next_mm = -1, noise_pos = 0, status = 1;
     if (valid) {
-#pragma unroll
-        for (int i = 0; i < NG; i++) c.set(H_Y + i, sd[(int64_t)(SD_X0 + i) * a.cap]);
-        meal.planned = sd[(int64_t)SD_PLANNED * a.cap];
-        meal.last_cho = sd[(int64_t)SD_LAST_CHO * a.cap];
-        meal.last_Qsto = sd[(int64_t)SD_LAST_QSTO * a.cap];
-        meal.last_food = sd[(int64_t)SD_LAST_FOOD * a.cap];
-        meal.eating = si[(int64_t)SI_EATING * a.cap];
         minute = si[(int64_t)SI_MINUTE * a.cap];
-        meal_pos = si[(int64_t)SI_MEAL_POS * a.cap];
-        next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
-    }
-    const int st_i = a.hw.st;
-    const double st = (double)st_i;
-    int par = 0, cho_buf = 0;
-    StepCount cnt{0, 0};
-    for (int k = 0; k < a.n_steps; k++) {
-        double CHO = 0.0;                                      // env.py:75-77, mean of the announced grams
-        for (int j = 0; j < st_i; j++) {                       // mini_step, env.py:48-64 (patient side)
-            double d = 0.0;
-            bool fed = false;
-            if (valid) {
-                double announced = 0.0;
-                if (a.step_meals) {
-                    announced = a.step_meals[(int64_t)j * a.n + e];
-                } else {
-                    while (next_mm >= 0 && next_mm < minute) {
-                        meal_pos++;
-                        next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
-                    }
-                    if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
-                }
-                CHO += announced / st;
-                c.set(M_CHOA + cho_buf, CHO);
-                const double to_eat = meal_machine(meal, announced, c(H_Y + 0), c(H_Y + 1));
-                d = to_eat * 1000.0;                                         // t1dpatient.py:121
-                const double Dbar = meal.last_Qsto + meal.last_food * 1000.0;
-                fed = Dbar > 0.0;
-                if (fed) {                                                   // t1dpatient.py:136-140
-                    c.set(H_aa, 5.0 / 2.0 / (1.0 - c(H_b)) / Dbar);
-                    c.set(H_cc, 5.0 / 2.0 / c(H_d) / Dbar);
-                    c.set(H_bD, c(H_b) * Dbar);
-                    c.set(H_dD, c(H_d) * Dbar);
-                }
-            }
-            minute_pair<0>(c, valid, d, fed, (double)minute, a.carry_h != 0, cnt, par);
-            minute++;
-            cho_buf ^= 1;                                      // role I may still be reading the other buffer
+        if (role == 0) {
+#pragma unroll
+            for (int i = 0; i < 5; i++) v.set(R_Y + i, sd[(int64_t)(SD_X0 + i) * a.cap]);
+            v.set(R_Y + 5, sd[(int64_t)(SD_X0 + 12) * a.cap]);
+            v.set(R_Y + 6, 0.0);
+            meal.planned = sd[(int64_t)SD_PLANNED * a.cap];
+            meal.last_cho = sd[(int64_t)SD_LAST_CHO * a.cap];
+            meal.last_Qsto = sd[(int64_t)SD_LAST_QSTO * a.cap];
+            meal.last_food = sd[(int64_t)SD_LAST_FOOD * a.cap];
+            meal.eating = si[(int64_t)SI_EATING * a.cap];
+            meal_pos = si[(int64_t)SI_MEAL_POS * a.cap];
+            next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+        } else {
+#pragma unroll
+            for (int i = 0; i < NS; i++) v.set(R_Y + i, sd[(int64_t)(SD_X0 + 5 + i) * a.cap]);
+            c.set(M_LAST_CGM, sd[(int64_t)SD_LAST_CGM * a.cap]);
+            noise_pos = si[(int64_t)SI_NOISE_POS * a.cap];
+            status = si[(int64_t)SI_STATUS * a.cap];
         }
     }
-    if (valid) {
-#pragma unroll
-        for (int i = 0; i < NG; i++) sd[(int64_t)(SD_X0 + i) * a.cap] = c(H_Y + i);
-        sd[(int64_t)SD_PLANNED * a.cap] = meal.planned;
-        sd[(int64_t)SD_LAST_CHO * a.cap] = meal.last_cho;
-        sd[(int64_t)SD_LAST_QSTO * a.cap] = meal.last_Qsto;
-        sd[(int64_t)SD_LAST_FOOD * a.cap] = meal.last_food;
-        si[(int64_t)SI_EATING * a.cap] = meal.eating;
-        si[(int64_t)SI_MEAL_POS * a.cap] = meal_pos;
-    }
-}
-
-// ---- role I: insulin side of the patient + the closed loop around it (env.py:66-117) -----------------------
-__device__ __forceinline__ void episode_i(const EpisodeArgs &a, const int64_t e, const bool valid, const Col &c)
-{
-    double *sd = a.sd + e;
-    int32_t *si = a.si + e;
-    int minute = 0, noise_pos = 0, status = 1;
-    if (valid) {
-#pragma unroll
-        for (int i = 0; i < NI; i++) c.set(H_Y + NG + i, sd[(int64_t)(SD_X0 + NG + i) * a.cap]);
-        c.set(M_HCARRY, sd[(int64_t)SD_H_CARRY * a.cap]);
-        c.set(M_LAST_CGM, sd[(int64_t)SD_LAST_CGM * a.cap]);
-        minute = si[(int64_t)SI_MINUTE * a.cap];
-        noise_pos = si[(int64_t)SI_NOISE_POS * a.cap];
-        status = si[(int64_t)SI_STATUS * a.cap];
-    }
-    int step_nstep = 0, step_nrej = 0;
     const int st_i = a.hw.st;
     const double st = (double)st_i;
-    int par = 0, cho_buf = 0;
+    int par = 0, cho_buf = 0, step_nstep = 0, step_nrej = 0;
 
     for (int k = 0; k < a.n_steps; k++) {
-        double ins_kg = 0.0;
-        if (valid) {
+        double u = 0.0, CHO = 0.0, BG = 0.0, CGM = 0.0;
+        bool fed = false;
+        if (role == 1 && valid) {
             // ---- controller.policy(observation, reward, done, **info) ----
             double a_basal = 0.0, a_bolus = 0.0;
             double ctrl[NCTRL];
@@ -486,7 +433,7 @@ __device__ __forceinline__ void episode_i(const EpisodeArgs &a, const int64_t e,
             // ---- env.step, env.py:66-117 ----
             const double ins = pump_quantise(a_basal, a.hw.pump[0], a.hw.pump[1], a.hw.pump[2]) +
                                pump_quantise(a_bolus, a.hw.pump[3], a.hw.pump[4], a.hw.pump[5]);
-            ins_kg = ins * 6000.0 / c(H_BW);                // t1dpatient.py:122
+            u = ins * 6000.0 / c(H_BW);                     // t1dpatient.py:122
             // the pump command is constant over the env-step: its mean (env.py:78) does not wait for the minutes
             double insulin = 0.0;
             for (int j = 0; j < st_i; j++) insulin += ins / st;
@@ -494,61 +441,96 @@ __device__ __forceinline__ void episode_i(const EpisodeArgs &a, const int64_t e,
                 double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
                 r[3 * a.n] = insulin; r[10 * a.n] = a_basal; r[11 * a.n] = a_bolus;
             }
-            c.set(M_BG, 0.0); c.set(M_CGM, 0.0);
         }
-        for (int j = 0; j < st_i; j++) {                   // mini_step, env.py:48-64 (sensor side)
+        for (int j = 0; j < st_i; j++) {                   // mini_step, env.py:48-64
+            if (role == 0 && valid) {
+                double announced = 0.0;
+                if (a.step_meals) {                        // scenario.get_action evaluated by the caller
+                    announced = a.step_meals[(int64_t)j * a.n + e];
+                } else {
+                    while (next_mm >= 0 && next_mm < minute) {
+                        meal_pos++;
+                        next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+                    }
+                    if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
+                }
+                CHO += announced / st;
+                c.set(M_CHOA + cho_buf, CHO);
+                const double to_eat = meal_machine(meal, announced, v(R_Y + 0), v(R_Y + 1));
+                u = to_eat * 1000.0;                                         // t1dpatient.py:121
+                const double Dbar = meal.last_Qsto + meal.last_food * 1000.0;
+                fed = Dbar > 0.0;
+                if (fed) {                                                   // t1dpatient.py:136-140
+                    c.set(H_aa, 5.0 / 2.0 / (1.0 - c(H_b)) / Dbar);
+                    c.set(H_cc, 5.0 / 2.0 / c(H_d) / Dbar);
+                    c.set(H_bD, c(H_b) * Dbar);
+                    c.set(H_dD, c(H_d) * Dbar);
+                }
+            }
             StepCount cnt{0, 0};
-            const int idid = minute_pair<1>(c, valid, ins_kg, false, (double)minute, a.carry_h != 0, cnt, par);
-            cho_buf ^= 1;
-            if (!valid) continue;
-            if (idid < 0 && status > 0) status = idid;
-            if (a.counters) {
-                const int64_t row = (int64_t)(k * st_i + j) * 2;
-                a.counters[row * a.n + e] = cnt.nstep;
-                a.counters[(row + 1) * a.n + e] = cnt.nrej;
-            }
-            step_nstep += cnt.nstep;
-            step_nrej += cnt.nrej;
+            const int idid = minute_pair(c, v, role, valid, u, fed, (double)minute, a.carry_h != 0,
+                                         sd + (int64_t)SD_H_CARRY * a.cap, cnt, par);
             minute++;
-            const double bg = c(H_Y + 12) / c(H_Vg);                            // t1dpatient.py:217-218
-            double last_cgm = c(M_LAST_CGM);
-            if (minute % st_i == 0) {                                           // cgm.py:27
-                last_cgm = cgm_sample(a, e, bg, noise_pos);
-                c.set(M_LAST_CGM, last_cgm);
+            cho_buf ^= 1;                                      // role I may still be reading the other buffer
+            if (role == 1 && valid) {
+                if (idid < 0 && status > 0) status = idid;
+                if (a.counters) {
+                    const int64_t row = (int64_t)(k * st_i + j) * 2;
+                    a.counters[row * a.n + e] = cnt.nstep;
+                    a.counters[(row + 1) * a.n + e] = cnt.nrej;
+                }
+                step_nstep += cnt.nstep;
+                step_nrej += cnt.nrej;
+                const double bg = c(R_Y + 5) / c(H_Vg);                         // x12 / Vg, t1dpatient.py:217-218
+                double last_cgm = c(M_LAST_CGM);
+                if (minute % st_i == 0) {                                       // cgm.py:27
+                    last_cgm = cgm_sample(a, e, bg, noise_pos);
+                    c.set(M_LAST_CGM, last_cgm);
+                }
+                BG += bg / st; CGM += last_cgm / st;
             }
-            c.set(M_BG, c(M_BG) + bg / st);
-            c.set(M_CGM, c(M_CGM) + last_cgm / st);
         }
-        if (!valid) continue;
-        const double BG = c(M_BG), CGM = c(M_CGM);
-        const double CHO = c(M_CHOA + (cho_buf ^ 1));                    // published by role G in the last minute
-        const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
-        double lbgi, hbgi, ri, r_prev, r_now, t0, t1;
-        risk_index(BG, lbgi, hbgi, ri);                                  // env.py:85
-        risk_index(cgm_prev, t0, t1, r_prev);                            // risk_diff, env.py:27-33
-        risk_index(CGM, t0, t1, r_now);
-        const double reward = r_prev - r_now;
-        const bool done = (BG < 70.0) || (BG > 350.0);                   // env.py:103
-        sd[(int64_t)SD_CGM_PREV * a.cap] = CGM;
-        sd[(int64_t)SD_OBS * a.cap] = CGM;
-        sd[(int64_t)SD_INFO_MEAL * a.cap] = CHO;
-        stats_add_row_resident(a.stats + e, a.cap, BG, lbgi, hbgi, ri, reward, done, step_nstep, step_nrej);
-        step_nstep = 0; step_nrej = 0;
-        if (a.trace) {
-            double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
-            r[0 * a.n] = BG; r[1 * a.n] = CGM; r[2 * a.n] = CHO;
-            r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = CGM;
-            r[8 * a.n] = reward; r[9 * a.n] = done ? 1.0 : 0.0;
+        if (role == 1 && valid) {
+            CHO = c(M_CHOA + (cho_buf ^ 1));                                 // published by role G in the last minute
+            const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
+            double lbgi, hbgi, ri, r_prev, r_now, t0, t1;
+            risk_index(BG, lbgi, hbgi, ri);                                  // env.py:85
+            risk_index(cgm_prev, t0, t1, r_prev);                            // risk_diff, env.py:27-33
+            risk_index(CGM, t0, t1, r_now);
+            const double reward = r_prev - r_now;
+            const bool done = (BG < 70.0) || (BG > 350.0);                   // env.py:103
+            sd[(int64_t)SD_CGM_PREV * a.cap] = CGM;
+            sd[(int64_t)SD_OBS * a.cap] = CGM;
+            sd[(int64_t)SD_INFO_MEAL * a.cap] = CHO;
+            stats_add_row_resident(a.stats + e, a.cap, BG, lbgi, hbgi, ri, reward, done, step_nstep, step_nrej);
+            step_nstep = 0; step_nrej = 0;
+            if (a.trace) {
+                double *r = a.trace + (int64_t)k * NTRACE * a.n + e;
+                r[0 * a.n] = BG; r[1 * a.n] = CGM; r[2 * a.n] = CHO;
+                r[4 * a.n] = lbgi; r[5 * a.n] = hbgi; r[6 * a.n] = ri; r[7 * a.n] = CGM;
+                r[8 * a.n] = reward; r[9 * a.n] = done ? 1.0 : 0.0;
+            }
         }
     }
     if (valid) {
+        if (role == 0) {
 #pragma unroll
-        for (int i = 0; i < NI; i++) sd[(int64_t)(SD_X0 + NG + i) * a.cap] = c(H_Y + NG + i);
-        sd[(int64_t)SD_H_CARRY * a.cap] = c(M_HCARRY);
-        sd[(int64_t)SD_LAST_CGM * a.cap] = c(M_LAST_CGM);
-        si[(int64_t)SI_MINUTE * a.cap] = minute;
-        si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
-        si[(int64_t)SI_STATUS * a.cap] = status;
+            for (int i = 0; i < 5; i++) sd[(int64_t)(SD_X0 + i) * a.cap] = v(R_Y + i);
+            sd[(int64_t)(SD_X0 + 12) * a.cap] = v(R_Y + 5);
+            sd[(int64_t)SD_PLANNED * a.cap] = meal.planned;
+            sd[(int64_t)SD_LAST_CHO * a.cap] = meal.last_cho;
+            sd[(int64_t)SD_LAST_QSTO * a.cap] = meal.last_Qsto;
+            sd[(int64_t)SD_LAST_FOOD * a.cap] = meal.last_food;
+            si[(int64_t)SI_EATING * a.cap] = meal.eating;
+            si[(int64_t)SI_MEAL_POS * a.cap] = meal_pos;
+        } else {
+#pragma unroll
+            for (int i = 0; i < NS; i++) sd[(int64_t)(SD_X0 + 5 + i) * a.cap] = v(R_Y + i);
+            sd[(int64_t)SD_LAST_CGM * a.cap] = c(M_LAST_CGM);
+            si[(int64_t)SI_MINUTE * a.cap] = minute;
+            si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
+            si[(int64_t)SI_STATUS * a.cap] = status;
+        }
     }
 }
 
@@ -563,8 +545,7 @@ __global__ void __launch_bounds__(pair::PBLOCK, 8) run_pair_kernel(const Episode
     const pair::Col c{smem + lane};
     if (role == 0 && valid) stage_params(c, param_source(a, e));
     __syncthreads();
-    if (role == 0) pair::episode_g(a, e, valid, c);
-    else pair::episode_i(a, e, valid, c);
+    pair::episode_pair(a, e, valid, role, c);
 }
 
 cudaError_t launch_run_pair(const EpisodeArgs &a, cudaStream_t s)
