@@ -49,6 +49,9 @@ def parse():
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='target duration of the cpu_baseline sample')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--shards', type=int, default=0,
+                    help='host-resident shards of the e2e leg (engine.run_shards); 0 = one resident wave each '
+                         '(148 SMs x 256 episodes = 1262 seed groups)')
     return ap.parse_args()
 
 
@@ -316,21 +319,26 @@ def main():
     # ---- end to end: host buffers in, statistics out, through the public API ----
     e2e = None
     if not args.no_e2e:
-        noise_h = torch.empty(noise.shape, dtype=torch.float64).pin_memory()
-        mm_h = torch.empty(mm.shape, dtype=torch.int32).pin_memory()
-        mg_h = torch.empty(mg.shape, dtype=torch.float64).pin_memory()
-        rows_hp = torch.empty(rows.shape, dtype=torch.int32).pin_memory()
-        noise_h.copy_(noise); mm_h.copy_(mm); mg_h.copy_(mg); rows_hp.copy_(rows)
-        stats_h = torch.empty(_capi.NSTAT, E, dtype=torch.float64).pin_memory()
-        agg_h = torch.empty(_capi.NSTAT, dtype=torch.float64).pin_memory()
-        h2d = noise_h.numel() * 8 + mm_h.numel() * 4 + mg_h.numel() * 8 + rows_hp.numel() * 4
-        d2h = stats_h.numel() * 8 + agg_h.numel() * 8
+        # the population lives in pinned host memory as shards of whole seed groups (public API: engine.run_shards,
+        # which uploads shard k+1 on one stream while shard k computes on another)
+        from simglucose_b200.engine import run_shards
+        n_sh = max(1, min(args.shards or int(round(args.groups / 1262.0)), args.groups))
+        cuts = [30 * (args.groups * i // n_sh) for i in range(n_sh + 1)]
+        shards, h2d = [], 0
+        for lo, hi in zip(cuts[:-1], cuts[1:]):
+            sh = {'patient_row': rows[lo:hi], 'noise': noise[:, lo:hi], 'meal_minute': mm[:, lo:hi],
+                  'meal_grams': mg[:, lo:hi], 'ctrl_rows': ctrl_rows[:, lo:hi]}
+            sh = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory().copy_(v) for k, v in sh.items()}
+            h2d += sum(v.numel() * v.element_size() for v in sh.values())
+            shards.append(sh)
+        stats_h = [torch.empty(_capi.NSTAT, hi - lo, dtype=torch.float64).pin_memory()
+                   for lo, hi in zip(cuts[:-1], cuts[1:])]
+        d2h = sum(t.numel() * 8 for t in stats_h) + n_sh * _capi.NSTAT * 8
+        e2e_agg = [None]
 
         def e2e_pass():
-            eng.reset(rows_hp, noise_h, mm_h, mg_h, row0=False)          # uploads inside
-            eng.run(n_steps, controller='bb', ctrl_rows=ctrl_rows, trace=False)
-            stats_h.copy_(eng.stats(), non_blocking=True)
-            agg_h.copy_(eng.reduce_stats(agg), non_blocking=True)
+            _, e2e_agg[0] = run_shards(shards, n_steps, controller='bb', device=local, slots=2, stats_out=stats_h,
+                                       carry_h=args.carry_h, fma=args.fma)
             torch.cuda.synchronize()
         e2e_pass()
         barrier()
@@ -347,7 +355,8 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         e2e = {'value': world * E * n_min * n_e2e / (float(ms.item()) * 1e-3), 'unit': METRIC,
                'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h), 'steps': n_e2e,
-               'wall_s': time.perf_counter() - t0}
+               'wall_s': time.perf_counter() - t0, 'api': 'simglucose_b200.engine.run_shards',
+               'shards': n_sh, 'rows_check': float(e2e_agg[0][0])}
 
     cpu = None
     if rank == 0 and not args.no_cpu:

@@ -177,3 +177,35 @@ def test_step_cap_compaction_is_bit_identical(controller):
         lock = run(6, lockstep=True)
         assert torch.equal(torch.nan_to_num(lock[0]), torch.nan_to_num(base[0]))
         assert torch.equal(lock[2], base[2]) and torch.equal(lock[3], base[3])
+
+
+def test_run_shards_streams_host_population_identically():
+    """engine.run_shards (host-resident shards, upload of shard k+1 overlapped with the kernel of shard k on a second
+    stream) == one resident batch, bit for bit, and its aggregate == the reduction of the per-episode statistics."""
+    import torch
+    from simglucose_b200 import params as P
+    from simglucose_b200.engine import BatchEngine, run_shards
+    E, n_steps = 30 * 500, 96
+    rows, noise, mm, mg = _cohort_inputs(E, n_steps, seed=4)
+    q = torch.from_numpy(P.quest_table()).cuda()[rows.long()]
+    cr = torch.stack([torch.full_like(q[:, 0], 140.0), q[:, 0], q[:, 1], torch.zeros_like(q[:, 0])])
+    eng = BatchEngine(E)
+    eng.reset(rows, noise, mm, mg, row0=False)
+    eng.run(n_steps, controller='bb', ctrl_rows=cr, trace=False)
+    want = eng.stats().cpu()
+    agg_want = eng.reduce_stats().cpu().numpy()
+    eng.close()
+    cuts = [0, 30 * 100, 30 * 101, 30 * 333, E]                      # ragged shards, one of a single seed group
+    shards = []
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        sh = {'patient_row': rows[lo:hi], 'noise': noise[:, lo:hi], 'meal_minute': mm[:, lo:hi],
+              'meal_grams': mg[:, lo:hi], 'ctrl_rows': cr[:, lo:hi]}
+        shards.append({k: v.cpu().contiguous().pin_memory() for k, v in sh.items()})
+    stats, agg = run_shards(shards, n_steps, controller='bb', slots=2)
+    got = torch.cat(stats, dim=1)
+    assert torch.equal(got, want)
+    assert agg[0] == agg_want[0] and agg[2] == agg_want[2] and agg[3] == agg_want[3] and agg[13] == agg_want[13]
+    for k in (8, 9, 10, 11, 12, 14, 15):
+        assert agg[k] == agg_want[k]
+    for k in (1, 4, 5, 6, 7):
+        assert abs(agg[k] - agg_want[k]) <= 1e-9 * max(1.0, abs(agg_want[k]))
