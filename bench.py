@@ -319,9 +319,9 @@ def main():
     # ---- end to end: host buffers in, statistics out, through the public API ----
     e2e = None
     if not args.no_e2e:
-        # the population lives in pinned host memory as shards of whole seed groups (public API: engine.run_shards,
+        # the population lives in pinned host memory as shards of whole seed groups (public API: engine.ShardRunner,
         # which uploads shard k+1 on one stream while shard k computes on another)
-        from simglucose_b200.engine import run_shards
+        from simglucose_b200.engine import ShardRunner
         n_sh = max(1, min(args.shards or int(round(args.groups / 1262.0)), args.groups))
         cuts = [30 * (args.groups * i // n_sh) for i in range(n_sh + 1)]
         shards, h2d = [], 0
@@ -335,10 +335,11 @@ def main():
                    for lo, hi in zip(cuts[:-1], cuts[1:])]
         d2h = sum(t.numel() * 8 for t in stats_h) + n_sh * _capi.NSTAT * 8
         e2e_agg = [None]
+        runner = ShardRunner(max(hi - lo for lo, hi in zip(cuts[:-1], cuts[1:])), device=local, slots=2,
+                             carry_h=args.carry_h, fma=args.fma)
 
         def e2e_pass():
-            _, e2e_agg[0] = run_shards(shards, n_steps, controller='bb', device=local, slots=2, stats_out=stats_h,
-                                       carry_h=args.carry_h, fma=args.fma)
+            _, e2e_agg[0] = runner.run(shards, n_steps, controller='bb', stats_out=stats_h)
             torch.cuda.synchronize()
         e2e_pass()
         barrier()
@@ -355,8 +356,9 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         e2e = {'value': world * E * n_min * n_e2e / (float(ms.item()) * 1e-3), 'unit': METRIC,
                'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h), 'steps': n_e2e,
-               'wall_s': time.perf_counter() - t0, 'api': 'simglucose_b200.engine.run_shards',
+               'wall_s': time.perf_counter() - t0, 'api': 'simglucose_b200.engine.ShardRunner.run',
                'shards': n_sh, 'rows_check': float(e2e_agg[0][0])}
+        runner.close()
 
     cpu = None
     if rank == 0 and not args.no_cpu:

@@ -267,48 +267,64 @@ class BatchEngine:
             pass
 
 
-def run_shards(shards, n_steps, controller='bb', ctrl=None, device=0, slots=2, stats_out=None, **engine_kw):
+class ShardRunner:
     """batch_sim for a population that lives in HOST memory as shards of episodes (sim_engine.py:65-76 hands the
     pathos pool one SimObj at a time; here a shard is the unit).  Shard k+1 is uploaded on one CUDA stream while
     shard k is simulated on another: `slots` engines, one stream each, so the host->device copies (8 bytes of
     sensor noise per env-step per episode dominate) hide behind the episode kernel and the tail of one shard's
-    launch overlaps the head of the next.
+    launch overlaps the head of the next.  Engines and streams live as long as the runner, so that repeated
+    populations reuse their device buffers (PyTorch caches device blocks per stream)."""
 
-    shards: iterable of dicts with host tensors / arrays, structure-of-arrays [rows, E_k] (pinned memory makes the
-      copies asynchronous): patient_row [E_k], noise [n_steps + 2, E_k], meal_minute / meal_grams [M, E_k] and
-      optionally ctrl_rows [4, E_k], x0 [13, E_k], params [32, E_k].
-    stats_out: optional list of pinned [NSTAT, E_k] tensors that receive the per-episode statistics.
-    Returns (stats_out, aggregate) -- aggregate is the population statistics vector [NSTAT] (numpy): sums, BG
-    extrema (rows 2, 3), episodes that reported done (row 13)."""
-    shards = list(shards)
-    dev = torch.device('cuda', device)
-    cap = max(int(torch.as_tensor(s['patient_row']).numel()) for s in shards)
-    slots = max(1, min(int(slots), len(shards)))
-    engines = [BatchEngine(cap, device=device, **engine_kw) for _ in range(slots)]
-    streams = [torch.cuda.Stream(device=dev) for _ in range(slots)]
-    if stats_out is None:
-        stats_out = [torch.empty(_capi.NSTAT, int(torch.as_tensor(s['patient_row']).numel()), dtype=torch.float64).pin_memory()
-                     for s in shards]
-    aggs = torch.empty(len(shards), _capi.NSTAT, dtype=torch.float64).pin_memory()
-    here = torch.cuda.current_stream(dev)
-    try:
-        for st in streams:
+    def __init__(self, capacity, device=0, slots=2, **engine_kw):
+        self.device = torch.device('cuda', device)
+        self.capacity = int(capacity)
+        self.engines = [BatchEngine(self.capacity, device=device, **engine_kw) for _ in range(max(1, int(slots)))]
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in self.engines]
+
+    def run(self, shards, n_steps, controller='bb', ctrl=None, stats_out=None):
+        """shards: iterable of dicts with host tensors / arrays, structure-of-arrays [rows, E_k] (pinned memory makes
+          the copies asynchronous): patient_row [E_k], noise [n_steps + 2, E_k], meal_minute / meal_grams [M, E_k]
+          and optionally ctrl_rows [4, E_k], x0 [13, E_k], params [32, E_k].
+        stats_out: optional list of pinned [NSTAT, E_k] tensors that receive the per-episode statistics.
+        Returns (stats_out, aggregate) -- aggregate is the population statistics vector [NSTAT] (numpy): sums, BG
+        extrema (rows 2, 3), episodes that reported done (row 13)."""
+        shards = list(shards)
+        if stats_out is None:
+            stats_out = [torch.empty(_capi.NSTAT, int(torch.as_tensor(s['patient_row']).numel()),
+                                     dtype=torch.float64).pin_memory() for s in shards]
+        aggs = torch.empty(len(shards), _capi.NSTAT, dtype=torch.float64).pin_memory()
+        here = torch.cuda.current_stream(self.device)
+        for st in self.streams:
             st.wait_stream(here)
+        n = len(self.engines)
         for k, sh in enumerate(shards):
-            eng, st = engines[k % slots], streams[k % slots]
+            eng, st = self.engines[k % n], self.streams[k % n]
             with torch.cuda.stream(st):
                 eng.reset(sh['patient_row'], sh['noise'], sh.get('meal_minute'), sh.get('meal_grams'),
                           x0=sh.get('x0'), params=sh.get('params'), row0=False)
                 eng.run(n_steps, controller=controller, ctrl=ctrl, ctrl_rows=sh.get('ctrl_rows'), trace=False)
                 stats_out[k].copy_(eng.stats(), non_blocking=True)
                 aggs[k].copy_(eng.reduce_stats(), non_blocking=True)
-        for st in streams:
+        for st in self.streams:
             here.wait_stream(st)
             st.synchronize()
-    finally:
-        for eng in engines:
+        a = aggs.numpy()
+        agg = a.sum(axis=0)
+        agg[2], agg[3] = a[:, 2].min(), a[:, 3].max()
+        return stats_out, agg
+
+    def close(self):
+        for eng in self.engines:
             eng.close()
-    a = aggs.numpy()
-    agg = a.sum(axis=0)
-    agg[2], agg[3] = a[:, 2].min(), a[:, 3].max()
-    return stats_out, agg
+        self.engines = []
+
+
+def run_shards(shards, n_steps, controller='bb', ctrl=None, device=0, slots=2, stats_out=None, **engine_kw):
+    """One-shot ShardRunner: see ShardRunner.run for the shard format and the return value."""
+    shards = list(shards)
+    cap = max(int(torch.as_tensor(s['patient_row']).numel()) for s in shards)
+    runner = ShardRunner(cap, device=device, slots=min(int(slots), len(shards)), **engine_kw)
+    try:
+        return runner.run(shards, n_steps, controller=controller, ctrl=ctrl, stats_out=stats_out)
+    finally:
+        runner.close()

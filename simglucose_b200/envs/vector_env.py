@@ -28,13 +28,18 @@ _T = {name: i for i, name in enumerate(_capi.TRACE_COLS)}
 class T1DSimVecEnv(object):
     def __init__(self, num_envs, patient_names=None, seed=0, start_hour=0, horizon_steps=480, sensor='Dexcom',
                  pump='Insulet', stream_mode='device', group_size=1, params=None, x0=None, auto_reset=False,
-                 device=0, carry_h=False, fma=False, episode_offset=0, step_cap=None):
+                 device=0, carry_h=False, fma=False, episode_offset=0, step_cap=None, reward_fun=None):
         """patient_names: list of names / 1-based ids cycled over the environments (default: the 30 virtual
         patients in table order).  params [32, E] / x0 [13, E]: per-environment overrides (perturbed
         populations).  group_size: environments per shared stream (the reference shares RandomScenario(seed)
         and CGMSensor(seed) across the patients of one batch_sim).  step_cap: heavy-minute compaction
         (BatchEngine.set_step_cap) for step(); default 5 when every environment has a meal schedule of its own
-        (group_size == 1) and the population is large enough for the second launch to pay (>= 524,288), else off."""
+        (group_size == 1) and the population is large enough for the second launch to pay (>= 524,288), else off.
+        reward_fun: None = risk_diff fused into the step kernel (env.py:27-33), or a callable
+        reward_fun(BG_last_hour) -> [E] tensor, the reference's custom-reward hook (env.py:66, 100-102) batched:
+        BG_last_hour is the device tensor CGM_hist[-int(60 / sample_time):], shape [n <= window, E], oldest first
+        (the reset sample included, as in the reference); it is a view of `self.cgm_window`, valid until the next
+        step."""
         self.num_envs = int(num_envs)
         self.engine = BatchEngine(self.num_envs, device=device, carry_h=carry_h, fma=fma, sensor=sensor, pump=pump)
         self.device = self.engine.device
@@ -59,6 +64,11 @@ class T1DSimVecEnv(object):
         self._row = torch.empty(_capi.NTRACE, self.num_envs, dtype=torch.float64, device=self.device)
         self.steps = None
         self.max_basal = float(self.engine.pump['max_basal'])
+        self.reward_fun = reward_fun
+        self.window_size = int(60 / self.sample_time)                      # env.py:100
+        self.cgm_window = (torch.zeros(self.window_size, self.num_envs, dtype=torch.float64, device=self.device)
+                           if reward_fun is not None else None)
+        self._window_n = 0
 
     # -- streams -----------------------------------------------------------------------------------------------
     def _make_streams(self):
@@ -91,6 +101,9 @@ class T1DSimVecEnv(object):
         self.steps = 0
         self._epoch += 1
         self.info = self._info(row0, reset=True)
+        if self.cgm_window is not None:
+            self.cgm_window[-1] = row0[_T['CGM']]                          # CGM_hist[0], env.py:129
+            self._window_n = 1
         return row0[_T['obs']]
 
     def _info(self, row, reset=False):
@@ -120,7 +133,14 @@ class T1DSimVecEnv(object):
         row = self.engine.step(basal, bolus, out=self._row)
         self.steps += 1
         self.info = self._info(row)
-        return row[_T['obs']], row[_T['reward']], row[_T['done']] != 0, self.info
+        reward = row[_T['reward']]
+        if self.cgm_window is not None:                                    # env.py:96, 100-102
+            w = self.cgm_window
+            w[:-1] = w[1:].clone()
+            w[-1] = row[_T['CGM']]
+            self._window_n = min(self._window_n + 1, self.window_size)
+            reward = self.reward_fun(w[self.window_size - self._window_n:])
+        return row[_T['obs']], reward, row[_T['done']] != 0, self.info
 
     def rollout(self, n_steps, controller='bb', ctrl=None, ctrl_rows=None, actions=None, trace=False):
         """n_steps env-steps in ONE launch with the controller evaluated on device ('bb', 'pid') or a

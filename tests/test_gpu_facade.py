@@ -349,6 +349,38 @@ def test_vector_env_device_streams():
     a.close(); b.close()
 
 
+def test_vector_env_custom_reward_window():
+    """reward_fun hook of the vector env (env.py:66, 100-102): the callable sees CGM_hist[-20:] as a [n, E] device
+    tensor, oldest first, reset sample included.  A tensor restatement of risk_diff (env.py:27-33) through the
+    device risk kernel must reproduce the fused reward; a window statistic checks length and order."""
+    import torch
+    from simglucose_b200 import ops
+    from simglucose_b200.envs import T1DSimVecEnv
+    seen = []
+
+    def risk_diff_t(w):
+        seen.append(w.clone())
+        if w.shape[0] < 2:
+            return torch.zeros(w.shape[1], dtype=torch.float64, device=w.device)
+        return ops.risk_index_elementwise(w[-2])[2] - ops.risk_index_elementwise(w[-1])[2]
+
+    a = T1DSimVecEnv(90, seed=3, horizon_steps=30, group_size=30)
+    b = T1DSimVecEnv(90, seed=3, horizon_steps=30, group_size=30, reward_fun=risk_diff_t)
+    a.reset(); b.reset()
+    assert b.window_size == 20
+    basal = torch.full((90,), 0.012, dtype=torch.float64, device=a.device)
+    hist = [b.info['cgm'].clone()]
+    for k in range(30):
+        _, ra, _, _ = a.step(basal)
+        _, rb, _, info = b.step(basal)
+        hist.append(info['cgm'].clone())
+        assert torch.allclose(ra, rb, rtol=0, atol=1e-12)
+        w = seen[-1]
+        want = torch.stack(hist[-20:])
+        assert w.shape[0] == min(k + 2, 20) and torch.equal(w, want)
+    a.close(); b.close()
+
+
 def test_simulate_keyword_interface(tmp_path):
     """user_interface.simulate(...) with every argument given (tests/test_ui.py of the reference drives the same
     call through mocked prompts): per-patient CSVs + the three report CSVs; numbers == the cohort fixture."""

@@ -6,7 +6,7 @@ OUT=gpurun_out/$TAG
 mkdir -p $OUT
 timeout 600 python -m pytest tests/test_gpu_scale.py -x -q -k run_shards > $OUT/pytest.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/rc.txt
 tail -5 $OUT/pytest.log
-for n in 1 4 7 8 16; do
+for n in 1 7 14; do
   timeout 600 python bench.py --no-cpu --steps 2 --shards $n > $OUT/bench_$n.json 2> $OUT/bench_$n.err
   python - <<PY
 import json
