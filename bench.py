@@ -35,6 +35,25 @@ F_MISC = 40                                # pump, meal machine, CGM, risk/3, co
 METRIC = 'patient-sim-minutes/sec'
 
 
+_OUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly one JSON line: keep a private handle on it and point fd 1 at stderr, so that banners
+    printed by libraries (NCCL prints its version with printf at communicator creation) land on stderr."""
+    global _OUT
+    if _OUT is None:
+        sys.stdout.flush()
+        _OUT = os.fdopen(os.dup(1), 'w')
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _OUT or sys.stdout
+    out.write(json.dumps(line) + '\n')
+    out.flush()
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -203,11 +222,12 @@ def run_reference(args, rank, world):
                        'episodes': w['E'], 'minutes_per_episode': n_min, 'carry_h': bool(args.carry_h)},
             'cpu_baseline': cpu,
             'e2e': {'value': v, 'unit': METRIC, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():
     args = parse()
+    claim_stdout()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
@@ -383,7 +403,7 @@ def main():
                 'population': {'mean_bg': float(aa[1] / aa[0]), 'min_bg': float(aa[2]), 'max_bg': float(aa[3]),
                                'time_in_range': float(aa[10] / aa[0]), 'episodes_done': float(aa[13]),
                                'rows': float(aa[0])}}
-        print(json.dumps(line))
+        emit(line)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
