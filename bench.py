@@ -65,6 +65,7 @@ def parse():
     ap.add_argument('--days', type=int, default=3)
     ap.add_argument('--fma', action='store_true', help='SG_FLAG_FMA kernels (not the default arithmetic)')
     ap.add_argument('--carry-h', action='store_true')
+    ap.add_argument('--fp32', action='store_true', help='optional FP32 mode (SG_FLAG_FP32): NOT the graded arithmetic')
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='target duration of the cpu_baseline sample')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
@@ -259,7 +260,7 @@ def main():
     # inputs resident in HBM before the timed region
     noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=1, episode_offset=ep0, group_size=30, device=dev)
     mm, mg = S.device_scenarios(E, n_min, start_minute=0, seed=1, episode_offset=ep0, group_size=30, device=dev)
-    eng = BatchEngine(E, device=local, carry_h=args.carry_h, fma=args.fma)
+    eng = BatchEngine(E, device=local, carry_h=args.carry_h, fma=args.fma, fp32=args.fp32)
     agg = torch.zeros(_capi.NSTAT, dtype=torch.float64, device=dev)
 
     def one_pass():
@@ -356,7 +357,7 @@ def main():
         d2h = sum(t.numel() * 8 for t in stats_h) + n_sh * _capi.NSTAT * 8
         e2e_agg = [None]
         runner = ShardRunner(max(hi - lo for lo, hi in zip(cuts[:-1], cuts[1:])), device=local, slots=2,
-                             carry_h=args.carry_h, fma=args.fma)
+                             carry_h=args.carry_h, fma=args.fma, fp32=args.fp32)
 
         def e2e_pass():
             _, e2e_agg[0] = runner.run(shards, n_steps, controller='bb', stats_out=stats_h)
@@ -392,10 +393,11 @@ def main():
         aa = agg_all.cpu().numpy()
         line = {'metric': METRIC, 'value': value, 'unit': METRIC, 'n_gpus': world, 'steps': args.steps,
                 'warmup': args.warmup, 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
-                'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+                'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if args.fp32 else 'f64', 'data': 'synthetic',
                 'config': {'workload': 'configs[1] cohort: 30 virtual patients x %d seed groups per GPU x %d-day '
                                        'RandomScenario, BBController, Dexcom, Insulet' % (args.groups, args.days),
-                           'episodes_per_gpu': E, 'minutes_per_episode': n_min, 'arithmetic': 'fma' if args.fma else 'strict (no FMA contraction)',
+                           'episodes_per_gpu': E, 'minutes_per_episode': n_min, 'arithmetic': ('fp32 integrator (optional mode, looser bound)' if args.fp32 else
+                                          'fma' if args.fma else 'strict (no FMA contraction)'),
                            'carry_h': bool(args.carry_h), 'parallelism': 'episodes sharded, dp%d' % world,
                            'l2': 'inputs (%.1f GB noise per GPU) larger than L2' % (noise.numel() * 8 / 1e9)},
                 'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': int(launches),

@@ -25,7 +25,7 @@ TRACE_COLS = ['BG', 'CGM', 'CHO', 'insulin', 'LBGI', 'HBGI', 'Risk', 'obs', 'rew
 STAT_COLS = ['rows', 'sum_bg', 'min_bg', 'max_bg', 'sum_lbgi', 'sum_hbgi', 'sum_risk', 'sum_reward', 'lt50',
              'lt70', 'inrange', 'gt180', 'gt250', 'first_done', 'dopri_steps', 'dopri_rejects']
 CTRL_ACTIONS, CTRL_BB, CTRL_PID = 0, 1, 2
-FLAG_CARRY_H, FLAG_FMA, FLAG_PAIR = 1, 2, 4
+FLAG_CARRY_H, FLAG_FMA, FLAG_PAIR, FLAG_FP32 = 1, 2, 4, 8
 
 # every symbol include/simglucose_b200.h declares
 SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_hardware', 'sg_load_params',

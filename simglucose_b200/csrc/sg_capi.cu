@@ -225,7 +225,9 @@ static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, co
         return SG_OK;
     }
     cudaError_t ce;
-    if (h->flags & SG_FLAG_PAIR)
+    if (h->flags & SG_FLAG_FP32)
+        ce = sg_fma::launch_run_fp32(a, (cudaStream_t)stream);
+    else if (h->flags & SG_FLAG_PAIR)
         ce = use_fma(h) ? sg_fma::launch_run_pair(a, (cudaStream_t)stream) : sg_strict::launch_run_pair(a, (cudaStream_t)stream);
     else
         ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream) : sg_strict::launch_run(a, (cudaStream_t)stream);

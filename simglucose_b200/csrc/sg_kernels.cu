@@ -607,6 +607,9 @@ cudaError_t launch_run_capped(const EpisodeArgs &a, cudaStream_t s)
 }
 
 #include "sg_pair.cuh"
+#ifdef SG_WITH_FP32
+#include "sg_fp32.cuh"
+#endif
 
 cudaError_t launch_patient_step(const PatientArgs &a, cudaStream_t s)
 {

@@ -145,3 +145,4 @@ struct ReduceArgs {
 
 SG_DECLARE_LAUNCHERS(sg_strict)
 SG_DECLARE_LAUNCHERS(sg_fma)
+namespace sg_fma { cudaError_t launch_run_fp32(const sgk::EpisodeArgs &a, cudaStream_t s); }   // built with FMA contraction only

@@ -28,14 +28,14 @@ class BatchEngine:
     T1DSimEnv (simulation/env.py:36-180) driven by SimObj.simulate (simulation/sim_engine.py:29-39).
     """
 
-    def __init__(self, capacity, device=0, carry_h=False, fma=False, sensor='Dexcom', pump='Insulet', pair=False):
+    def __init__(self, capacity, device=0, carry_h=False, fma=False, sensor='Dexcom', pump='Insulet', pair=False, fp32=False):
         if not torch.cuda.is_available():
             raise _capi.SgError('simglucose_b200 needs a CUDA device (there is no CPU fallback)')
         self.lib = _capi.load()
         self.device = torch.device('cuda', device)
         self.capacity = int(capacity)
         self.flags = ((_capi.FLAG_CARRY_H if carry_h else 0) | (_capi.FLAG_FMA if fma else 0) |
-                      (_capi.FLAG_PAIR if pair else 0))
+                      (_capi.FLAG_PAIR if pair else 0) | (_capi.FLAG_FP32 if fp32 else 0))
         h = C.c_void_p()
         _capi.check(self.lib.sg_create(self.device.index, self.capacity, self.flags, C.byref(h)))
         self._h = h

