@@ -170,7 +170,10 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
 
     const int st_i = a.hw.st;
     const double st = (double)st_i;
+    // x / st (env.py:75-81) through the refined reciprocal: bit-identical to the IEEE quotient (sg_math.cuh div_r)
+    const double r_st = sgm::rcp_nr(st);
     int next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+    bool have_rprev = false;                           // H_RPREV holds risk_index(CGM_hist[-1]) from the step before
 
     // ---- minute put aside (phases A / B) ----
     Suspend sp{0.0, 0.0, 0.0, 0, 0, 0, 0};
@@ -181,7 +184,7 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
         const int32_t *di = a.defer_i + e;
 #pragma unroll
         for (int i = 0; i < NX; i++) c.set(H_K1 + i, dd[(int64_t)i * a.cap]);
-        sp.h = dd[(int64_t)13 * a.cap]; sp.x = dd[(int64_t)14 * a.cap]; sp.facold = dd[(int64_t)15 * a.cap];
+        sp.h = dd[(int64_t)13 * a.cap]; sp.x = dd[(int64_t)14 * a.cap]; sp.lfacold = dd[(int64_t)15 * a.cap];
         r_ins = dd[(int64_t)16 * a.cap]; r_announced = dd[(int64_t)17 * a.cap];
         r_CHO = dd[(int64_t)18 * a.cap]; r_insulin = dd[(int64_t)19 * a.cap];
         r_BG = dd[(int64_t)20 * a.cap]; r_CGM = dd[(int64_t)21 * a.cap];
@@ -194,7 +197,6 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
         // ---- controller.policy(observation, reward, done, **info) ----
         double a_basal = 0.0, a_bolus = 0.0;
         double ins, CHO = 0.0, insulin = 0.0, BG = 0.0, CGM = 0.0;
-        const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
         if (MODE == RUN_RESUME) {
             ins = r_ins; CHO = r_CHO; insulin = r_insulin; BG = r_BG; CGM = r_CGM;
         } else {
@@ -232,6 +234,8 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
         }
         }
         bool aside = false;                            // RUN_CAPPED: this lane's minute was put aside
+        const double ins_kg = ins * 6000.0 / c(H_BW);  // t1dpatient.py:122, constant over the env-step
+        const double ins_mean = sgm::div_r(ins, st, r_st);
         for (int j = 0; j < st_i; j++) {               // mini_step, env.py:48-64
             int mode = MINUTE_FRESH;
             if (MODE == RUN_CAPPED && aside) mode = MINUTE_IDLE;
@@ -254,7 +258,7 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
             if (!DEFER || mode != MINUTE_IDLE) {
                 const double to_eat = (DEFER && mode == MINUTE_RESUME) ? meal.last_cho
                                                                         : meal_machine(meal, announced, x[0], x[1]);
-                m = minute_setup(c, to_eat, ins, meal.last_Qsto, meal.last_food);
+                m = minute_setup_rate(c, to_eat, ins_kg, meal.last_Qsto, meal.last_food);
             }
             StepCount cnt{0, 0};
             const int idid = dopri5_minute<BLOCK, DEFER>(c, m, x, (double)minute, a.carry_h != 0, h_carry, cnt, lanes,
@@ -267,7 +271,7 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
                 int32_t *di = a.defer_i + e;
 #pragma unroll
                 for (int i = 0; i < NX; i++) dd[(int64_t)i * a.cap] = c(H_K1 + i);
-                dd[(int64_t)13 * a.cap] = sp.h; dd[(int64_t)14 * a.cap] = sp.x; dd[(int64_t)15 * a.cap] = sp.facold;
+                dd[(int64_t)13 * a.cap] = sp.h; dd[(int64_t)14 * a.cap] = sp.x; dd[(int64_t)15 * a.cap] = sp.lfacold;
                 dd[(int64_t)16 * a.cap] = ins; dd[(int64_t)17 * a.cap] = announced;
                 dd[(int64_t)18 * a.cap] = CHO; dd[(int64_t)19 * a.cap] = insulin;
                 dd[(int64_t)20 * a.cap] = BG; dd[(int64_t)21 * a.cap] = CGM;
@@ -286,15 +290,22 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
             step_nstep += cnt.nstep;
             step_nrej += cnt.nrej;
             minute++;
-            const double bg = x[12] / c(H_Vg);                          // t1dpatient.py:217-218
+            const double bg = sgm::div_r(x[12], c(H_Vg), c(H_rVg));      // t1dpatient.py:217-218
             if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
-            CHO += announced / st; insulin += ins / st; BG += bg / st; CGM += last_cgm / st;
+            CHO += sgm::div_r(announced, st, r_st); insulin += ins_mean;
+            BG += sgm::div_r(bg, st, r_st); CGM += sgm::div_r(last_cgm, st, r_st);
         }
         if (MODE == RUN_CAPPED && aside) continue;     // phase B closes this env-step
         double lbgi, hbgi, ri, r_prev, r_now, t0, t1;
         risk_index(BG, lbgi, hbgi, ri);                                  // env.py:85
-        risk_index(cgm_prev, t0, t1, r_prev);                            // risk_diff, env.py:27-33
+        if (have_rprev) {
+            r_prev = c(H_RPREV);
+        } else {
+            risk_index(sd[(int64_t)SD_CGM_PREV * a.cap], t0, t1, r_prev);    // risk_diff, env.py:27-33
+        }
         risk_index(CGM, t0, t1, r_now);
+        c.set(H_RPREV, r_now);
+        have_rprev = true;
         const double reward = r_prev - r_now;
         const bool done = (BG < 70.0) || (BG > 350.0);                   // env.py:103
         sd[(int64_t)SD_CGM_PREV * a.cap] = CGM;

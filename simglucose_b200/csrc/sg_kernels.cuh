@@ -35,7 +35,7 @@ constexpr int NTRACE = 12;
 constexpr int NSTAT = 16;
 constexpr int NCTRL = 4;
 constexpr int BLOCK = 64;
-// scratch rows of an episode whose minute was put aside: k1[13], h, x, facold, ins, announced, CHO, insulin, BG, CGM
+// scratch rows of an episode whose minute was put aside: k1[13], h, x, log(facold), ins, announced, CHO, insulin, BG, CGM
 constexpr int DEFER_ND = 22;
 // nstep, naccpt, nrej, reject, minute index inside the env-step, steps / rejects of the env-step so far
 constexpr int DEFER_NI = 7;

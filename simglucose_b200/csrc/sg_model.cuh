@@ -36,6 +36,10 @@ enum Hoisted {
     H_aa, H_cc, H_bD, H_dD,
     // refined reciprocals of constant divisors (sgm::rcp_nr): x / BW and x / Vi cost 3 instructions
     H_rBW, H_rVi,
+    // per-minute / per-env-step bookkeeping kept out of registers: reciprocal of Vg (BG = x12 / Vg every minute), the
+    // Dbar the H_aa..H_dD rows were computed for, the risk index of the previous env-step's CGM (risk_diff)
+    H_rVg, H_Dbar, H_RPREV,
+    H_L4,                      // log of 1e-4, the floor of DOPCOR's facold (step_control works on logarithms)
     // per-thread scratch vectors of the integrator: k1 of the current step (needed again only after a
     // rejected step and by HINIT) and the two longest-lived stage accumulators (see dopri5_minute)
     H_K1, H_P7 = H_K1 + 13, H_PE = H_P7 + 13,
@@ -80,6 +84,8 @@ __device__ __forceinline__ void stage_params(const Column<BLOCK> &c, Load p)
     c.set(H_kd, kd); c.set(H_ksc, p(P_ksc)); c.set(H_Vg, p(P_Vg));
     c.set(H_aa, 0.0); c.set(H_cc, 0.0); c.set(H_bD, 0.0); c.set(H_dD, 0.0);
     c.set(H_rBW, sgm::rcp_nr(p(P_BW))); c.set(H_rVi, sgm::rcp_nr(p(P_Vi)));
+    c.set(H_rVg, sgm::rcp_nr(p(P_Vg))); c.set(H_Dbar, 0.0); c.set(H_RPREV, 0.0);
+    c.set(H_L4, sgm::log_pos(1.0e-4));
 }
 
 // Inputs of the ODE that are constant over one simulated minute (t1dpatient.py:110:
@@ -89,6 +95,28 @@ struct Minute {
     double ins;    // action.insulin * 6000 / BW             t1dpatient.py:122
     bool fed;      // Dbar > 0                               t1dpatient.py:130,135
 };
+
+// ins_per_kg: action.insulin * 6000 / BW (constant over an env-step: the caller divides once).
+template <int BLOCK>
+__device__ __forceinline__ Minute minute_setup_rate(const Column<BLOCK> &c, double cho, double ins_per_kg,
+                                                    double last_Qsto, double last_food)
+{
+    Minute m;
+    m.d = cho * 1000.0;
+    m.ins = ins_per_kg;
+    const double Dbar = last_Qsto + last_food * 1000.0;
+    m.fed = Dbar > 0.0;
+    // Dbar only moves while the patient eats: the four quotients / products below are recomputed when it did
+    // (same inputs, same results -- the cache cannot change a bit)
+    if (m.fed && Dbar != c(H_Dbar)) {                       // t1dpatient.py:136-140
+        c.set(H_Dbar, Dbar);
+        c.set(H_aa, 5.0 / 2.0 / (1.0 - c(H_b)) / Dbar);
+        c.set(H_cc, 5.0 / 2.0 / c(H_d) / Dbar);
+        c.set(H_bD, c(H_b) * Dbar);
+        c.set(H_dD, c(H_d) * Dbar);
+    }
+    return m;
+}
 
 template <int BLOCK>
 __device__ __forceinline__ Minute minute_setup(const Column<BLOCK> &c, double cho, double insulin,
@@ -260,7 +288,7 @@ struct StepCount { int nstep, nrej; };
 // costs up to 36 steps against 3 -- are finished by a second kernel over the compacted list of such episodes, so
 // that the other 31 lanes of the warp do not wait for them).  k1 of the step travels in the H_K1 slots.
 struct Suspend {
-    double h, x, facold;
+    double h, x, lfacold;
     int nstep, naccpt, nrej, reject;
 };
 enum MinuteMode { MINUTE_IDLE = 0, MINUTE_FRESH = 1, MINUTE_RESUME = 2 };
@@ -285,8 +313,10 @@ __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
         const double a = sgm::div_r(c(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
         dnf = dnf + a * a;
         dny = dny + b * b;
+        c.set(H_PE + i, r);                                  // the second half divides by the same scale
     }
-    double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+    // dny / dnf through div_nr: bit-identical for these operands (both above 1e-10)
+    double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(sgm::div_nr(dny, dnf)) * 0.01;
     h = fmin(h, hmax);
     return HinitGuess{h, dnf};
 }
@@ -300,29 +330,33 @@ __device__ __noinline__ double hinit_second(double *col, double h, double dnf, d
 #pragma unroll 1
     for (int i = 0; i < NX; i++) {
         const double sk = ATOL + RTOL * fabs(c(H_Y + i));
-        const double a = sgm::div_nr(c(H_P7 + i) - c(H_K1 + i), sk);
+        const double a = sgm::div_r(c(H_P7 + i) - c(H_K1 + i), sk, c(H_PE + i));   // reciprocal left by the first half
         der2 = der2 + a * a;
     }
-    der2 = sqrt(der2) / h;
+    der2 = sgm::div_nr(sqrt(der2), h);                       // h >= 1e-6
     const double der12 = fmax(fabs(der2), sqrt(dnf));
-    const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3) : sgm::pow_pos(0.01 / der12, 1.0 / 5.0);
+    const double h1 = (der12 <= 1e-15) ? fmax(1.0e-6, fabs(h) * 1.0e-3)
+                                       : sgm::pow_pos(sgm::div_nr(0.01, sgm::min_sel(der12, 1e300)), 1.0 / 5.0);
     return fmin(fmin(100.0 * fabs(h), h1), hmax);
 }
 
-struct StepControl { double err, hnew_accept, hnew_reject; };
+struct StepControl { double err, hnew_accept, hnew_reject, lerr; };
 
 // Step-size controller of DOPCOR (Lund stabilisation, beta = 0.04) from the summed squared scaled errors.
-static __device__ __noinline__ StepControl step_control(double errsum, double facold, double h)
+// lfacold: log of facold (log_pos).  Returns the log of err as well: the caller keeps it as the next lfacold.
+static __device__ __noinline__ StepControl step_control(double errsum, double lfacold, double h)
 {
     const double beta = 0.04, safe = 0.9;
     const double expo1 = 0.2 - beta * 0.75;
     const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
     const double err = sqrt(sgm::div_nr(errsum, (double)NX));
-    const double fac11 = sgm::pow_pos(err, expo1);
-    double fac = sgm::div_nr(fac11, sgm::pow_pos(facold, beta));
+    const double lerr = sgm::log_pos(err);
+    const double fac11 = sgm::pow_of_log(lerr, expo1);
+    double fac = sgm::div_nr(fac11, sgm::pow_of_log(lfacold, beta));
     fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
     StepControl r;
     r.err = err;
+    r.lerr = lerr;
     r.hnew_accept = sgm::div_nr(h, fac);
     r.hnew_reject = sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
     return r;
@@ -356,7 +390,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     double x = t0;
     const double xend = t0 + 1.0;
     const double hmax = fabs(xend - t0);
-    double facold = 1.0e-4;
+    double lfacold = c(H_L4);                          // facold = 1e-4
     bool last = false, reject = false;
     int nstep = 0, naccpt = 0, idid = 0, phase = PH_K1;
     double yt[NX], kt[NX], P4[NX], P5[NX], P6[NX];
@@ -368,7 +402,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         for (int i = 0; i < NX; i++) { yt[i] = y[i]; c.set(H_Y + i, y[i]); }
     }
     if (DEFER && mode == MINUTE_RESUME) {
-        h = sp->h; x = sp->x; facold = sp->facold;
+        h = sp->h; x = sp->x; lfacold = sp->lfacold;
         nstep = sp->nstep; naccpt = sp->naccpt; cnt.nrej = sp->nrej; reject = sp->reject != 0;
         phase = PH_RESUME;
     }
@@ -470,11 +504,11 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 const double a = sgm::div_nr(e, sk);
                 err = err + a * a;
             }
-            const StepControl sc = step_control(err, facold, h);
+            const StepControl sc = step_control(err, lfacold, h);
             err = sc.err;
             double hnew = sc.hnew_accept;
             if (err <= 1.0) {
-                facold = sgm::max_sel(err, 1.0e-4);
+                lfacold = (err > 1.0e-4) ? sc.lerr : c(H_L4);        // facold = max(err, 1e-4)
                 naccpt++;
 #pragma unroll
                 for (int i = 0; i < NX; i++) c.set(H_Y + i, yt[i]);   // kt is k1 of the next step (FSAL)
@@ -503,7 +537,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             if (DEFER && cap > 0 && nstep >= cap) {          // put the rest of this minute aside
 #pragma unroll
                 for (int i = 0; i < NX; i++) c.set(H_K1 + i, kt[i]);
-                sp->h = h; sp->x = x; sp->facold = facold;
+                sp->h = h; sp->x = x; sp->lfacold = lfacold;
                 sp->nstep = nstep; sp->naccpt = naccpt; sp->nrej = cnt.nrej; sp->reject = reject ? 1 : 0;
                 idid = IDID_SUSPENDED;
             }

@@ -133,7 +133,7 @@ static __device__ __noinline__ double hinit_second_all(double *col, double h, do
 
 // Integrator control state of role I.
 struct Ctl {
-    double x, xend, facold, dnf;
+    double x, xend, lfacold, dnf;
     int nstep, naccpt, nrej, idid;
     bool last, reject;
 };
@@ -151,15 +151,15 @@ __device__ __forceinline__ int begin_step(Ctl &s, double &h)
 }
 
 // Error estimate of a finished step -> accept / reject, next step size (DOPCOR).  Returns the action bits.
-__device__ __forceinline__ int control_step(Ctl &s, double errsum, double &h)
+__device__ __forceinline__ int control_step(Ctl &s, double errsum, double &h, double l4)
 {
-    const StepControl sc = step_control(errsum, s.facold, h);
+    const StepControl sc = step_control(errsum, s.lfacold, h);
     const double err = sc.err;
     double hnew = sc.hnew_accept;
     bool begin = false;
     int code;
     if (err <= 1.0) {
-        s.facold = sgm::max_sel(err, 1.0e-4);
+        s.lfacold = (err > 1.0e-4) ? sc.lerr : l4;           // facold = max(err, 1e-4)
         s.naccpt++;
         code = ACT_COMMIT;                                   // kt is k1 of the next step (FSAL)
         s.x = s.x + h;
@@ -200,7 +200,7 @@ __device__ __forceinline__ int minute_pair(const Col &c, const Col &v, const int
     double (&sq)[NS] = P5;
     double h = 0.0;
     int idid = valid ? 0 : 1, phase = PH_K1;
-    Ctl s{t0, t0 + 1.0, 1.0e-4, 0.0, 0, 0, 0, 0, false, false};
+    Ctl s{t0, t0 + 1.0, c(H_L4), 0.0, 0, 0, 0, 0, false, false};
 
     if (valid) {
 #pragma unroll
@@ -314,7 +314,7 @@ __device__ __forceinline__ int minute_pair(const Col &c, const Col &v, const int
 #pragma unroll
                     for (int i = 0; i < NS; i++) err = err + sq[i];
                     err = err + c(R_PE + 5);
-                    code = control_step(s, err, h);
+                    code = control_step(s, err, h, c(H_L4));
                 }
                 c.set(M_H, h);
                 c.set(M_ACT, (double)code);
