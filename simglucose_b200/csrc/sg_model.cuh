@@ -305,7 +305,7 @@ __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
 {
     const Column<BLOCK> c{col};
     double dny = 0.0, dnf = 0.0;
-#pragma unroll 1
+#pragma unroll 4
     for (int i = 0; i < NX; i++) {
         const double yi = c(H_Y + i);
         const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
@@ -327,7 +327,7 @@ __device__ __noinline__ double hinit_second(double *col, double h, double dnf, d
 {
     const Column<BLOCK> c{col};
     double der2 = 0.0;
-#pragma unroll 1
+#pragma unroll 4
     for (int i = 0; i < NX; i++) {
         const double sk = ATOL + RTOL * fabs(c(H_Y + i));
         const double a = sgm::div_r(c(H_P7 + i) - c(H_K1 + i), sk, c(H_PE + i));   // reciprocal left by the first half

@@ -28,23 +28,26 @@ _T = {name: i for i, name in enumerate(_capi.TRACE_COLS)}
 class T1DSimVecEnv(object):
     def __init__(self, num_envs, patient_names=None, seed=0, start_hour=0, horizon_steps=480, sensor='Dexcom',
                  pump='Insulet', stream_mode='device', group_size=1, params=None, x0=None, auto_reset=False,
-                 device=0, carry_h=False, fma=False, episode_offset=0, step_cap=None, reward_fun=None):
+                 device=0, carry_h=False, fma=False, episode_offset=0, step_cap=None, reward_fun=None, fp32=False):
         """patient_names: list of names / 1-based ids cycled over the environments (default: the 30 virtual
         patients in table order).  params [32, E] / x0 [13, E]: per-environment overrides (perturbed
         populations).  group_size: environments per shared stream (the reference shares RandomScenario(seed)
         and CGMSensor(seed) across the patients of one batch_sim).  step_cap: heavy-minute compaction
         (BatchEngine.set_step_cap) for step(); default 5 when every environment has a meal schedule of its own
         (group_size == 1) and the population is large enough for the second launch to pay (>= 524,288), else off.
+        fp32: the optional single-precision integrator (SG_FLAG_FP32; relative BG error <= 1e-3 per day, see
+        csrc/sg_fp32.cuh) -- for RL populations; the heavy-minute compaction does not apply to it.
         reward_fun: None = risk_diff fused into the step kernel (env.py:27-33), or a callable
         reward_fun(BG_last_hour) -> [E] tensor, the reference's custom-reward hook (env.py:66, 100-102) batched:
         BG_last_hour is the device tensor CGM_hist[-int(60 / sample_time):], shape [n <= window, E], oldest first
         (the reset sample included, as in the reference); it is a view of `self.cgm_window`, valid until the next
         step."""
         self.num_envs = int(num_envs)
-        self.engine = BatchEngine(self.num_envs, device=device, carry_h=carry_h, fma=fma, sensor=sensor, pump=pump)
+        self.engine = BatchEngine(self.num_envs, device=device, carry_h=carry_h, fma=fma, sensor=sensor, pump=pump,
+                                  fp32=fp32)
         self.device = self.engine.device
         self.sample_time = self.engine.sample_time
-        auto = 5 if (int(group_size) == 1 and self.num_envs >= 524288) else 0
+        auto = 5 if (int(group_size) == 1 and self.num_envs >= 524288 and not fp32) else 0
         self.step_cap = auto if step_cap is None else int(step_cap)
         self.engine.set_step_cap(self.step_cap)
         names = P.patient_names() if patient_names is None else list(patient_names)

@@ -41,9 +41,9 @@ def timed(fn, warm=1, reps=2):
     return e0.elapsed_time(e1) * 1e-3 / reps
 
 
-def config2(scale):
+def config2(scale, fp32=False):
     E, n_steps = int(1048576 * scale) // 64 * 64, 480
-    env = T1DSimVecEnv(E, seed=0, start_hour=0, horizon_steps=n_steps, stream_mode='device', group_size=1)
+    env = T1DSimVecEnv(E, seed=0, start_hour=0, horizon_steps=n_steps, stream_mode='device', group_size=1, fp32=fp32)
     basal = torch.empty(E, dtype=torch.float64, device=env.device)
     state = {'k': 0}
 
@@ -62,7 +62,8 @@ def config2(scale):
     agg = summarize(env.statistics())
     env.close()
     return {'config': 'configs[2] lockstep vector env, %d episodes x %d env-steps, basal ~ U(0, 0.05) U/min on device, '
-                      'risk_diff reward, no auto-reset, step_cap %d' % (E, n_steps, env.step_cap),
+                      'risk_diff reward, no auto-reset, step_cap %d%s' % (E, n_steps, env.step_cap,
+                                                                         ', OPTIONAL FP32 INTEGRATOR (not the graded arithmetic)' if fp32 else ''),
             'value': E * n_steps * 3 / sec, 'unit': 'patient-sim-minutes/sec', 'seconds': sec, 'env_steps_per_s': E * n_steps / sec,
             'gpu_launches': int(launches), 'ms_per_env_step': 1e3 * sec / n_steps, 'population': agg}
 
@@ -122,7 +123,7 @@ def main():
     args = ap.parse_args()
     assert torch.cuda.is_available(), 'needs a CUDA device (there is no CPU fallback)'
     _capi.load()
-    for name, fn in (('2', config2), ('3', config3), ('4', config4)):
+    for name, fn in (('2', config2), ('2f', lambda sc: config2(sc, fp32=True)), ('3', config3), ('4', config4)):
         if args.only and name not in args.only.split(','):
             continue
         print(json.dumps(fn(args.scale)), flush=True)

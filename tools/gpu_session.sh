@@ -13,6 +13,8 @@ timeout 600 python bench.py --fma --no-cpu > $OUT/bench_fma.json 2> $OUT/bench_f
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "bench_ref rc=$?" | tee -a $OUT/rc.txt
 timeout 600 python bench.py --carry-h --no-cpu > $OUT/bench_carry.json 2> $OUT/bench_carry.err; echo "bench_carry rc=$?" | tee -a $OUT/rc.txt
 timeout 600 python bench.py --impl reference --carry-h --steps 2 --warmup 1 > $OUT/bench_ref_carry.json 2> $OUT/bench_ref_carry.err; echo "bench_ref_carry rc=$?" | tee -a $OUT/rc.txt
+timeout 1500 python tools/bench_configs.py > $OUT/configs.jsonl 2> $OUT/configs.err; echo "configs rc=$?" | tee -a $OUT/rc.txt
+timeout 600 python bench.py --fp32 --no-cpu > $OUT/bench_fp32.json 2> $OUT/bench_fp32.err; echo "bench_fp32 rc=$?" | tee -a $OUT/rc.txt
 PROF="python bench.py --groups 1262 --days 1 --steps 1 --warmup 1 --no-cpu --no-e2e"
 timeout 300 $PROF > $OUT/prof_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/launches.csv $PROF > $OUT/ncu_launches.log 2>&1
