@@ -337,6 +337,12 @@ def main():
                         'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',
                         'algorithmic_bytes_per_launch': hbm_bytes}}
 
+    if args.fp32:                                     # the optional mode runs on the FP32 pipe: its own (nominal) ceiling
+        sm_ghz = 1.965
+        roofline.update({'bound': 'fp32', 'peak': 148 * 128 * 2 * sm_ghz / 1e3, 'frac': ach_tf / (148 * 128 * 2 * sm_ghz / 1e3),
+                         'kernel': 'run_fp32_kernel',
+                         'peak_source': 'nominal 148 SMs x 128 FP32 lanes x 2 flop x 1.965 GHz (optional mode, not graded)'})
+
     # ---- end to end: host buffers in, statistics out, through the public API ----
     e2e = None
     if not args.no_e2e:
