@@ -52,7 +52,7 @@ typedef enum { SG_OK = 0, SG_ERR_ARG = -1, SG_ERR_CUDA = -2, SG_ERR_STATE = -3, 
 #define SG_FLAG_FP32    8u   /* optional single-precision mode: the patient ODE and its DOPRI5 integration run in FP32
                                 (local time, uround 1.2e-7, rtol 1e-4, FMA); pump, sensor, meal machine, risk and
                                 statistics stay FP64.  Looser bound: max |dBG| / max(|BG|, 1) <= 1e-3 over a day against
-                                the FP64 path (tests/test_gpu_fp32.py; measured 8e-5).  Not the graded mode; ignored while a step cap is set. */
+                                the FP64 path (tests/test_gpu_fp32.py; measured 1.2e-4).  Not the graded mode; ignored while a step cap is set. */
 
 /* Controller fused into sg_run. */
 typedef enum {

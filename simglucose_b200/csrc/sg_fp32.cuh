@@ -7,7 +7,7 @@
 // machine, pump quantisation, sensor sampling, risk index, controllers, statistics) stays the FP64 code of
 // run_kernel.  It is meant for reinforcement-learning populations (configs[2]) where a relative BG error of
 // 1e-3 is far below sensor noise (Dexcom noise is several mg/dL); the bound is checked in tests/test_gpu_fp32.py
-// (measured: 8e-5 over a day, 2.4e-4 with step-size carry; 2.08e9 patient-min/s on the bench workload, s33).
+// (measured: 1.2e-4 over a day, 2.4e-4 with step-size carry; 2.64e9 patient-min/s on the bench workload, s37).
 //
 // What changes against the FP64 path, besides the type:
 //   * time inside integrate(t, t + 1) is local (0..1): the model is autonomous (t is unused, t1dpatient.py:119) and
@@ -53,7 +53,12 @@ __device__ __forceinline__ void rhs_f(const FCol &c, const FMinute &m, const flo
     dx[0] = -kmax * x[0] + m.d;
     float kgut = kmax;
     if (m.fed) {
-        const float t = tanhf(m.aa * (qsto - m.bD)) - tanhf(m.cc * (qsto - m.dD));
+        // tanh(u) - tanh(v) = 2 (e^2u - e^2v) / ((e^2u + 1)(e^2v + 1)) with hardware exp2 (2 ulp): ten instructions
+        // instead of two branchy tanhf; arguments clamped where tanh has saturated in single precision
+        const float u = fminf(fmaxf(2.0f * m.aa * (qsto - m.bD), -30.0f), 30.0f);
+        const float v = fminf(fmaxf(2.0f * m.cc * (qsto - m.dD), -30.0f), 30.0f);
+        const float eu = __expf(u), ev = __expf(v);
+        const float t = __fdividef(2.0f * (eu - ev), (eu + 1.0f) * (ev + 1.0f));
         kgut = c(F_kmin) + c(F_hk) * (t + 2.0f);
     }
     dx[1] = kmax * x[0] - x[1] * kgut;
@@ -176,12 +181,12 @@ __device__ __forceinline__ int dopri5_minute_f(const FCol &c, const FMinute &m, 
 #pragma unroll
         for (int i = 0; i < NX; i++) {
             const float e = h * (e1 * k1[i] + e3 * k3[i] + e4 * k4[i] + e5 * k5[i] + e6 * k6[i] + e7 * k2[i]);
-            const float a = e * __frcp_rn(atol + rtol * fmaxf(fabsf(y[i]), fabsf(yt[i])));
+            const float a = __fdividef(e, atol + rtol * fmaxf(fabsf(y[i]), fabsf(yt[i])));   // MUFU.RCP: 1 ulp is plenty here
             err += a * a;
         }
         err = sqrtf(err * (1.0f / NX));
-        const float fac11 = powf(err, expo1);
-        float fac = fac11 / powf(facold, beta);
+        const float fac11 = __powf(fmaxf(err, 1e-30f), expo1);      // step-size control needs a few digits only
+        float fac = __fdividef(fac11, __powf(facold, beta));
         fac = fmaxf(facc2, fminf(facc1, fac / safe));
         float hnew = h / fac;
         if (err <= 1.0f) {
@@ -245,7 +250,13 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
     int status = si[(int64_t)SI_STATUS * a.cap];
     const int st_i = a.hw.st;
     const double st = (double)st_i;
+    const double r_st = sgm::rcp_nr(st), r_Vg = sgm::rcp_nr(Vg);       // exact quotients through div_r, as in run_kernel
     int next_mm = (meal_pos < a.max_meals) ? a.meal_minute[(int64_t)meal_pos * a.n + e] : -1;
+    double Dbar_seen = 0.0, r_prev = 0.0;
+    bool have_rprev = false;
+    FMinute m;
+    m.d = m.ins = m.aa = m.cc = m.bD = m.dD = 0.0f;
+    m.fed = false;
 
     for (int k = 0; k < a.n_steps; k++) {
         // ---- controller.policy(observation, reward, done, **info) ----
@@ -254,7 +265,6 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
 #pragma unroll
         for (int i = 0; i < NCTRL; i++) ctrl[i] = a.ctrl_rows ? __ldg(a.ctrl_rows + (int64_t)i * a.n + e) : a.ctrl[i];
         const double obs = sd[(int64_t)SD_OBS * a.cap];
-        const double cgm_prev = sd[(int64_t)SD_CGM_PREV * a.cap];
         if (a.controller == 1) {                       // BBController._bb_policy
             const double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
             a_basal = p(P_u2ss) * BW / 6000.0;
@@ -278,6 +288,8 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
                            pump_quantise(a_bolus, a.hw.pump[3], a.hw.pump[4], a.hw.pump[5]);
         double CHO = 0.0, insulin = 0.0, BG = 0.0, CGM = 0.0;
         int step_nstep = 0, step_nrej = 0;
+        m.ins = (float)(ins * 6000.0 / BW);                                  // t1dpatient.py:122
+        const double ins_mean = sgm::div_r(ins, st, r_st);
         for (int j = 0; j < st_i; j++) {               // mini_step, env.py:48-64
             double announced = 0.0;
             if (a.step_meals) {
@@ -290,13 +302,11 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
                 if (next_mm == minute) announced = a.meal_grams[(int64_t)meal_pos * a.n + e];
             }
             const double to_eat = meal_machine(meal, announced, (double)x[0], (double)x[1]);
-            FMinute m;
             m.d = (float)(to_eat * 1000.0);                                  // t1dpatient.py:121
-            m.ins = (float)(ins * 6000.0 / BW);                              // t1dpatient.py:122
             const double Dbar = meal.last_Qsto + meal.last_food * 1000.0;    // t1dpatient.py:130
             m.fed = Dbar > 0.0;
-            m.aa = m.cc = m.bD = m.dD = 0.0f;
-            if (m.fed) {                                                     // t1dpatient.py:136-140
+            if (m.fed && Dbar != Dbar_seen) {                                // t1dpatient.py:136-140; Dbar only moves
+                Dbar_seen = Dbar;                                            // while the patient eats
                 m.aa = (float)(5.0 / 2.0 / (1.0 - bpar) / Dbar);
                 m.cc = (float)(5.0 / 2.0 / dpar / Dbar);
                 m.bD = (float)(bpar * Dbar);
@@ -313,15 +323,18 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
             step_nstep += cnt.nstep;
             step_nrej += cnt.nrej;
             minute++;
-            const double bg = (double)x[12] / Vg;                             // t1dpatient.py:217-218
+            const double bg = sgm::div_r((double)x[12], Vg, r_Vg);            // t1dpatient.py:217-218
             if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
-            CHO += announced / st; insulin += ins / st; BG += bg / st; CGM += last_cgm / st;
+            CHO += sgm::div_r(announced, st, r_st); insulin += ins_mean;
+            BG += sgm::div_r(bg, st, r_st); CGM += sgm::div_r(last_cgm, st, r_st);
         }
-        double lbgi, hbgi, ri, r_prev, r_now, t0, t1;
+        double lbgi, hbgi, ri, r_now, t0, t1;
         risk_index(BG, lbgi, hbgi, ri);                                  // env.py:85
-        risk_index(cgm_prev, t0, t1, r_prev);                            // risk_diff, env.py:27-33
+        if (!have_rprev) risk_index(sd[(int64_t)SD_CGM_PREV * a.cap], t0, t1, r_prev);   // risk_diff, env.py:27-33
         risk_index(CGM, t0, t1, r_now);
         const double reward = r_prev - r_now;
+        r_prev = r_now;
+        have_rprev = true;
         const bool done = (BG < 70.0) || (BG > 350.0);                   // env.py:103
         sd[(int64_t)SD_CGM_PREV * a.cap] = CGM;
         sd[(int64_t)SD_OBS * a.cap] = CGM;
