@@ -29,13 +29,16 @@ constexpr int NX = 13;
 
 // Per-episode constants staged in shared memory (one column per thread).
 enum Hoisted {
-    H_kmax = 0, H_kmin, H_hk, H_b, H_d, H_kabs, H_fk, H_BW, H_kp1, H_kp2, H_kp3, H_Fsnc,
-    H_ke1, H_ke2, H_k1, H_k2, H_Vm0, H_Vmx, H_Km0, H_m24, H_m1, H_ka1, H_ka2, H_Vi, H_p2u,
-    H_Ib, H_ki, H_m13, H_m2, H_kad, H_kd, H_ksc, H_Vg,
-    // per-minute values (rewritten by the owning thread at every minute start)
-    H_aa, H_cc, H_bD, H_dD,
-    // refined reciprocals of constant divisors (sgm::rcp_nr): x / BW and x / Vi cost 3 instructions
-    H_rBW, H_rVi,
+    // Rows 0 .. H_PAIR_END-1 are stored as PAIRS: the two values of rows (2k, 2k+1) of a thread are adjacent in shared
+    // memory, so that the RHS fetches them with one LDS.128 (Column::pair).  Pair partners are neighbours in the
+    // RHS's order of use.  aa..dD are per-minute values (rewritten when Dbar moves), rBW / rVi refined reciprocals
+    // of constant divisors (sgm::rcp_nr): x / BW and x / Vi cost 3 instructions.
+    H_aa = 0, H_bD, H_cc, H_dD, H_kmin, H_hk, H_kmax, H_kabs, H_fk, H_BW, H_rBW, H_kp1, H_kp2, H_kp3,
+    H_ke2, H_ke1, H_k1, H_k2, H_Fsnc, H_Km0, H_Vm0, H_Vmx, H_ka2, H_m2, H_m24, H_m1, H_ka1, H_m13,
+    H_Vi, H_rVi, H_p2u, H_ki, H_Ib, H_kd, H_kad, H_ksc,
+    H_PAIR_END,
+    // one value per row from here on
+    H_b = H_PAIR_END, H_d, H_Vg,
     // per-minute / per-env-step bookkeeping kept out of registers: reciprocal of Vg (BG = x12 / Vg every minute), the
     // Dbar the H_aa..H_dD rows were computed for, the risk index of the previous env-step's CGM (risk_diff)
     H_rVg, H_Dbar, H_RPREV,
@@ -56,13 +59,36 @@ enum Param {
     P_COUNT
 };
 
+static_assert(H_PAIR_END % 2 == 0, "paired rows come in twos");
+
 template <int BLOCK>
 struct Column {
-    double *base;   // &smem[threadIdx.x]
+    double *base;    // &smem[t]: rows H_PAIR_END.. of thread t at base[i * BLOCK] (consecutive lanes, consecutive words)
+    double *pbase;   // &smem[2 * t]: paired rows (2k, 2k+1) of thread t at pbase[2k * BLOCK + {0, 1}]
     // volatile: every use re-reads shared memory.  Without it ptxas keeps the ~35 parameters of the eight
     // inlined RHS copies in registers and spills Runge-Kutta stages to local memory instead.
-    __device__ __forceinline__ double operator()(int i) const { return ((const volatile double *)base)[i * BLOCK]; }
-    __device__ __forceinline__ void set(int i, double v) const { base[i * BLOCK] = v; }
+    __device__ __forceinline__ double operator()(int i) const
+    {
+        return i < H_PAIR_END ? ((const volatile double *)pbase)[(i & ~1) * BLOCK + (i & 1)]
+                              : ((const volatile double *)base)[i * BLOCK];
+    }
+    __device__ __forceinline__ void set(int i, double v) const
+    {
+        if (i < H_PAIR_END) pbase[(i & ~1) * BLOCK + (i & 1)] = v;
+        else base[i * BLOCK] = v;
+    }
+    // vector rows with an index the compiler cannot fold (rolled loops)
+    __device__ __forceinline__ double vec(int i) const { return ((const volatile double *)base)[i * BLOCK]; }
+    __device__ __forceinline__ void vec_set(int i, double v) const { base[i * BLOCK] = v; }
+    // rows (i, i + 1) of the paired region, i even: one 16-byte load
+    __device__ __forceinline__ double2 pair(int i) const
+    {
+        double2 r;
+        asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                     : "=d"(r.x), "=d"(r.y)
+                     : "r"((unsigned)__cvta_generic_to_shared(pbase + i * BLOCK)));
+        return r;
+    }
 };
 
 // Constants that only depend on the parameter row (t1dpatient.py:138,151,176,190,194: the
@@ -143,48 +169,53 @@ __device__ __forceinline__ double mask_nonneg(double x, double dx)
     return x >= 0.0 ? dx : 0.0;
 }
 
-// T1DPatient.model, t1dpatient.py:118-208.
+// T1DPatient.model, t1dpatient.py:118-208.  Parameters arrive two per shared-memory load (Column::pair).
 template <int BLOCK>
 __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, const double (&x)[NX],
                                     double (&dx)[NX])
 {
-    const double kmax = c(H_kmax);
+    const double2 kk = c.pair(H_kmax);                                      // kmax, kabs
+    const double kmax = kk.x;
     const double qsto = x[0] + x[1];                                        // :126
     dx[0] = -kmax * x[0] + m.d;                                             // :133
     double kgut;
     if (m.fed) {                                                            // :135-142
         // tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh)
-        const double tdiff = sgm::tanh_diff(c(H_aa) * (qsto - c(H_bD)), c(H_cc) * (qsto - c(H_dD)));
-        kgut = c(H_kmin) + c(H_hk) * (tdiff + 2.0);
+        const double2 ab = c.pair(H_aa), cd = c.pair(H_cc);                 // (aa, b*Dbar), (cc, d*Dbar)
+        const double tdiff = sgm::tanh_diff(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
+        const double2 kh = c.pair(H_kmin);                                  // kmin, (kmax - kmin) / 2
+        kgut = kh.x + kh.y * (tdiff + 2.0);
     } else {
         kgut = kmax;
     }
     dx[1] = kmax * x[0] - x[1] * kgut;                                      // :145
-    const double kabs = c(H_kabs);
-    dx[2] = kgut * x[1] - kabs * x[2];                                      // :148
-    const double Rat = sgm::div_r(c(H_fk) * x[2], c(H_BW), c(H_rBW));                            // :151
-    const double EGPt = c(H_kp1) - c(H_kp2) * x[3] - c(H_kp3) * x[8];       // :153
-    const double ke2 = c(H_ke2);
-    const double Et = (x[3] > ke2) ? c(H_ke1) * (x[3] - ke2) : 0.0;         // :158-161
+    dx[2] = kgut * x[1] - kk.y * x[2];                                      // :148
+    const double2 fb = c.pair(H_fk), rk = c.pair(H_rBW);                    // (f*kabs, BW), (1/BW, kp1)
+    const double Rat = sgm::div_r(fb.x * x[2], fb.y, rk.x);                 // :151
+    const double2 kp = c.pair(H_kp2);                                       // kp2, kp3
+    const double EGPt = rk.y - kp.x * x[3] - kp.y * x[8];                   // :153
+    const double2 ke = c.pair(H_ke2);                                       // ke2, ke1
+    const double Et = (x[3] > ke.x) ? ke.y * (x[3] - ke.x) : 0.0;           // :158-161
     const double egp = (0.0 > EGPt) ? 0.0 : EGPt;                           // max(EGPt, 0) :165
-    const double k1 = c(H_k1), k2 = c(H_k2);
-    dx[3] = mask_nonneg(x[3], egp + Rat - c(H_Fsnc) - Et - k1 * x[3] + k2 * x[4]);   // :165-167
-    const double Vmt = c(H_Vm0) + c(H_Vmx) * x[6];                          // :169
-    const double Uidt = sgm::div_nr(Vmt * x[4], c(H_Km0) + x[4]);                     // :171
-    dx[4] = mask_nonneg(x[4], -Uidt + k1 * x[3] - k2 * x[4]);               // :172-173
-    const double ka2 = c(H_ka2), m2 = c(H_m2);
-    dx[5] = mask_nonneg(x[5], -c(H_m24) * x[5] + c(H_m1) * x[9] + c(H_ka1) * x[10] + ka2 * x[11]);
-    const double It = sgm::div_r(x[5], c(H_Vi), c(H_rVi));                                     // :178
-    const double p2u = c(H_p2u), ki = c(H_ki);
-    dx[6] = -p2u * x[6] + p2u * (It - c(H_Ib));                             // :182
-    dx[7] = -ki * (x[7] - It);                                              // :185
-    dx[8] = -ki * (x[8] - x[7]);                                            // :187
-    dx[9] = mask_nonneg(x[9], -c(H_m13) * x[9] + m2 * x[5]);                // :190-191
-    const double kd = c(H_kd);
-    dx[10] = mask_nonneg(x[10], m.ins - c(H_kad) * x[10]);                  // :194-195
-    dx[11] = mask_nonneg(x[11], kd * x[10] - ka2 * x[11]);                  // :197-198
-    const double ksc = c(H_ksc);
-    dx[12] = mask_nonneg(x[12], -ksc * x[12] + ksc * x[3]);                 // :201-202
+    const double2 k12 = c.pair(H_k1), fk = c.pair(H_Fsnc);                  // (k1, k2), (Fsnc, Km0)
+    dx[3] = mask_nonneg(x[3], egp + Rat - fk.x - Et - k12.x * x[3] + k12.y * x[4]);   // :165-167
+    const double2 vm = c.pair(H_Vm0);                                       // Vm0, Vmx
+    const double Vmt = vm.x + vm.y * x[6];                                  // :169
+    const double Uidt = sgm::div_nr(Vmt * x[4], fk.y + x[4]);               // :171
+    dx[4] = mask_nonneg(x[4], -Uidt + k12.x * x[3] - k12.y * x[4]);         // :172-173
+    const double2 am = c.pair(H_ka2), mm = c.pair(H_m24), km = c.pair(H_ka1);   // (ka2, m2), (m2+m4, m1), (ka1, m1+m30)
+    dx[5] = mask_nonneg(x[5], -mm.x * x[5] + mm.y * x[9] + km.x * x[10] + am.x * x[11]);
+    const double2 vi = c.pair(H_Vi);                                        // Vi, 1/Vi
+    const double It = sgm::div_r(x[5], vi.x, vi.y);                         // :178
+    const double2 pk = c.pair(H_p2u), ik = c.pair(H_Ib);                    // (p2u, ki), (Ib, kd)
+    dx[6] = -pk.x * x[6] + pk.x * (It - ik.x);                              // :182
+    dx[7] = -pk.y * (x[7] - It);                                            // :185
+    dx[8] = -pk.y * (x[8] - x[7]);                                          // :187
+    dx[9] = mask_nonneg(x[9], -km.y * x[9] + am.y * x[5]);                  // :190-191
+    const double2 ak = c.pair(H_kad);                                       // ka1 + kd, ksc
+    dx[10] = mask_nonneg(x[10], m.ins - ak.x * x[10]);                      // :194-195
+    dx[11] = mask_nonneg(x[11], ik.y * x[10] - am.x * x[11]);               // :197-198
+    dx[12] = mask_nonneg(x[12], -ak.y * x[12] + ak.y * x[3]);               // :201-202
 }
 
 // InsulinPump.basal / .bolus, pump.py:23-39.  np.round == round-half-even == rint().
@@ -303,17 +334,17 @@ struct HinitGuess { double h, dnf; };
 template <int BLOCK>
 __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
 {
-    const Column<BLOCK> c{col};
+    const Column<BLOCK> c{col, nullptr};
     double dny = 0.0, dnf = 0.0;
 #pragma unroll 4
     for (int i = 0; i < NX; i++) {
-        const double yi = c(H_Y + i);
+        const double yi = c.vec(H_Y + i);
         const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
         const double sk = ATOL + RTOL * fabs(yi);
-        const double a = sgm::div_r(c(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
+        const double a = sgm::div_r(c.vec(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
         dnf = dnf + a * a;
         dny = dny + b * b;
-        c.set(H_PE + i, r);                                  // the second half divides by the same scale
+        c.vec_set(H_PE + i, r);                                  // the second half divides by the same scale
     }
     // dny / dnf through div_nr: bit-identical for these operands (both above 1e-10)
     double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(sgm::div_nr(dny, dnf)) * 0.01;
@@ -325,12 +356,12 @@ __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
 template <int BLOCK>
 __device__ __noinline__ double hinit_second(double *col, double h, double dnf, double hmax)
 {
-    const Column<BLOCK> c{col};
+    const Column<BLOCK> c{col, nullptr};
     double der2 = 0.0;
 #pragma unroll 4
     for (int i = 0; i < NX; i++) {
-        const double sk = ATOL + RTOL * fabs(c(H_Y + i));
-        const double a = sgm::div_r(c(H_P7 + i) - c(H_K1 + i), sk, c(H_PE + i));   // reciprocal left by the first half
+        const double sk = ATOL + RTOL * fabs(c.vec(H_Y + i));
+        const double a = sgm::div_r(c.vec(H_P7 + i) - c.vec(H_K1 + i), sk, c.vec(H_PE + i));   // reciprocal left by the first half
         der2 = der2 + a * a;
     }
     der2 = sgm::div_nr(sqrt(der2), h);                       // h >= 1e-6
