@@ -143,7 +143,7 @@ template <int MODE>
 __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_t e, const unsigned lanes, double *smem)
 {
     constexpr bool DEFER = MODE != RUN_PLAIN;
-    const Column<BLOCK> c{smem + threadIdx.x, smem + 2 * threadIdx.x};
+    const Column<BLOCK> c{smem + 2 * threadIdx.x};
     const ParamLoad p = param_source(a, e);
     stage_params(c, p);
 
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(BLOCK) patient_step_kernel(const PatientArgs p
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);
     if (e >= a.n) return;
-    const Column<BLOCK> c{smem + threadIdx.x, smem + 2 * threadIdx.x};
+    const Column<BLOCK> c{smem + 2 * threadIdx.x};
     const ParamLoad p = param_source(a, e);
     stage_params(c, p);
     double *sd = a.sd + e;
@@ -431,7 +431,7 @@ __global__ void __launch_bounds__(BLOCK) model_kernel(const ModelArgs a)
     extern __shared__ double smem[];
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     if (e >= a.n) return;
-    const Column<BLOCK> c{smem + threadIdx.x, smem + 2 * threadIdx.x};
+    const Column<BLOCK> c{smem + 2 * threadIdx.x};
     const ParamLoad p = a.params_soa ? ParamLoad{a.params_soa + e, a.n}
                                      : ParamLoad{a.table + (int64_t)a.patient_row[e] * P_COUNT, 1};
     stage_params(c, p);

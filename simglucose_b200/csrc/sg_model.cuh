@@ -37,19 +37,19 @@ enum Hoisted {
     H_ke2, H_ke1, H_k1, H_k2, H_Fsnc, H_Km0, H_Vm0, H_Vmx, H_ka2, H_m2, H_m24, H_m1, H_ka1, H_m13,
     H_Vi, H_rVi, H_p2u, H_ki, H_Ib, H_kd, H_kad, H_ksc,
     H_PAIR_END,
-    // one value per row from here on
     H_b = H_PAIR_END, H_d, H_Vg,
     // per-minute / per-env-step bookkeeping kept out of registers: reciprocal of Vg (BG = x12 / Vg every minute), the
     // Dbar the H_aa..H_dD rows were computed for, the risk index of the previous env-step's CGM (risk_diff)
     H_rVg, H_Dbar, H_RPREV,
     H_L4,                      // log of 1e-4, the floor of DOPCOR's facold (step_control works on logarithms)
-    // per-thread scratch vectors of the integrator: k1 of the current step (needed again only after a
-    // rejected step and by HINIT) and the two longest-lived stage accumulators (see dopri5_minute)
-    H_K1, H_P7 = H_K1 + 13, H_PE = H_P7 + 13,
-    // the accepted state y of the integrator (read once per stage, written once per accepted step)
-    H_Y = H_PE + 13,
-    H_COUNT = H_Y + 13
+    H_pad0,
+    // per-thread scratch vectors of the integrator, NV = 14 rows each (13 states + one pad row, so that states
+    // (2k, 2k+1) form a pair): k1 of the current step (needed again only after a rejected step and by HINIT), the two
+    // longest-lived stage accumulators (see dopri5_minute) and the accepted state y of the integrator
+    H_K1, H_P7 = H_K1 + 14, H_PE = H_P7 + 14, H_Y = H_PE + 14,
+    H_COUNT = H_Y + 14
 };
+constexpr int NV = 14;
 
 // Order of the parameter row handed over the C-ABI (include/simglucose_b200.h, sg_param).
 enum Param {
@@ -59,43 +59,43 @@ enum Param {
     P_COUNT
 };
 
-static_assert(H_PAIR_END % 2 == 0, "paired rows come in twos");
+static_assert(H_PAIR_END % 2 == 0 && H_K1 % 2 == 0 && H_COUNT % 2 == 0, "paired rows come in twos");
 
-template <int BLOCK>
+// The shared-memory column of one thread.
+//   PAIRED (the single-thread kernels): rows (2k, 2k+1) of thread t are adjacent -- base = &smem[2 * t], row i at
+//     base[(i & ~1) * BLOCK + (i & 1)] -- so that two parameters / two states move with one 16-byte access
+//     (pair / set_pair: a warp's 32 x 16 bytes are consecutive).  An 8-byte access in this layout costs twice the
+//     wavefronts, so the integrator loop only uses pairs.
+//   plain (the warp-pair kernel): base = &smem[t], row i at base[i * BLOCK].
+// volatile: every use re-reads shared memory.  Without it ptxas keeps the ~35 parameters of the eight inlined RHS
+// copies in registers and spills Runge-Kutta stages to local memory instead.
+template <int BLOCK, bool PAIRED = true>
 struct Column {
-    double *base;    // &smem[t]: rows H_PAIR_END.. of thread t at base[i * BLOCK] (consecutive lanes, consecutive words)
-    double *pbase;   // &smem[2 * t]: paired rows (2k, 2k+1) of thread t at pbase[2k * BLOCK + {0, 1}]
-    // volatile: every use re-reads shared memory.  Without it ptxas keeps the ~35 parameters of the eight
-    // inlined RHS copies in registers and spills Runge-Kutta stages to local memory instead.
-    __device__ __forceinline__ double operator()(int i) const
-    {
-        return i < H_PAIR_END ? ((const volatile double *)pbase)[(i & ~1) * BLOCK + (i & 1)]
-                              : ((const volatile double *)base)[i * BLOCK];
-    }
-    __device__ __forceinline__ void set(int i, double v) const
-    {
-        if (i < H_PAIR_END) pbase[(i & ~1) * BLOCK + (i & 1)] = v;
-        else base[i * BLOCK] = v;
-    }
-    // vector rows with an index the compiler cannot fold (rolled loops)
-    __device__ __forceinline__ double vec(int i) const { return ((const volatile double *)base)[i * BLOCK]; }
-    __device__ __forceinline__ void vec_set(int i, double v) const { base[i * BLOCK] = v; }
-    // rows (i, i + 1) of the paired region, i even: one 16-byte load
+    double *base;
+    static __device__ __forceinline__ int at(int i) { return PAIRED ? (i & ~1) * BLOCK + (i & 1) : i * BLOCK; }
+    __device__ __forceinline__ double operator()(int i) const { return ((const volatile double *)base)[at(i)]; }
+    __device__ __forceinline__ void set(int i, double v) const { base[at(i)] = v; }
+    // rows (i, i + 1), i even: one 16-byte access (PAIRED only)
     __device__ __forceinline__ double2 pair(int i) const
     {
         double2 r;
         asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
                      : "=d"(r.x), "=d"(r.y)
-                     : "r"((unsigned)__cvta_generic_to_shared(pbase + i * BLOCK)));
+                     : "r"((unsigned)__cvta_generic_to_shared(base + i * BLOCK)));
         return r;
+    }
+    __device__ __forceinline__ void set_pair(int i, double2 v) const
+    {
+        asm volatile("st.shared.v2.f64 [%0], {%1, %2};"
+                     :: "r"((unsigned)__cvta_generic_to_shared(base + i * BLOCK)), "d"(v.x), "d"(v.y) : "memory");
     }
 };
 
 // Constants that only depend on the parameter row (t1dpatient.py:138,151,176,190,194: the
 // sub-expressions (kmax-kmin)/2, f*kabs, m2+m4, m1+m30, ka1+kd are evaluated first by Python's
 // precedence, so hoisting them is bit-safe).
-template <int BLOCK, class Load>
-__device__ __forceinline__ void stage_params(const Column<BLOCK> &c, Load p)
+template <class ColT, class Load>
+__device__ __forceinline__ void stage_params(const ColT &c, Load p)
 {
     const double kmax = p(P_kmax), kmin = p(P_kmin), kabs = p(P_kabs);
     const double m1 = p(P_m1), m2 = p(P_m2), ka1 = p(P_ka1), kd = p(P_kd);
@@ -330,21 +330,54 @@ constexpr int IDID_SUSPENDED = 2;
 
 struct HinitGuess { double h, dnf; };
 
-// HINIT, first half: h = 0.01 * |y| / |k1| in the scaled norm.  Reads k1 (H_K1) and y (H_Y) from the column.
+// Loops over the 13 states two at a time (the pair layout of Column): i = 0, 2, .., 12; state i + 1 == 13 is the pad.
+#define SG_FOR_PAIRS(i) _Pragma("unroll") for (int i = 0; i < NV; i += 2)
+
+template <int BLOCK>
+__device__ __forceinline__ void store_vec(const Column<BLOCK> &c, int row, const double (&v)[NX])
+{
+    SG_FOR_PAIRS(i) c.set_pair(row + i, make_double2(v[i], (i + 1 < NX) ? v[i + 1 < NX ? i + 1 : i] : 0.0));
+}
+
+template <int BLOCK>
+__device__ __forceinline__ void load_vec(const Column<BLOCK> &c, int row, double (&v)[NX])
+{
+    SG_FOR_PAIRS(i) {
+        const double2 t = c.pair(row + i);
+        v[i] = t.x;
+        if (i + 1 < NX) v[i + 1 < NX ? i + 1 : i] = t.y;
+    }
+}
+
+// HINIT, first half: h = 0.01 * |y| / |k1| in the scaled norm.  Reads k1 (H_K1) and y (H_Y) from the column and
+// leaves the reciprocal scales in the H_PE rows for the second half.
 template <int BLOCK>
 __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
 {
-    const Column<BLOCK> c{col, nullptr};
+    const Column<BLOCK> c{col};
     double dny = 0.0, dnf = 0.0;
-#pragma unroll 4
-    for (int i = 0; i < NX; i++) {
-        const double yi = c.vec(H_Y + i);
-        const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
-        const double sk = ATOL + RTOL * fabs(yi);
-        const double a = sgm::div_r(c.vec(H_K1 + i), sk, r), b = sgm::div_r(yi, sk, r);
-        dnf = dnf + a * a;
-        dny = dny + b * b;
-        c.vec_set(H_PE + i, r);                                  // the second half divides by the same scale
+    SG_FOR_PAIRS(i) {
+        const double2 y2 = c.pair(H_Y + i), k2 = c.pair(H_K1 + i);
+        double2 r2 = make_double2(0.0, 0.0);
+        {
+            const double yi = y2.x;
+            const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
+            const double sk = ATOL + RTOL * fabs(yi);
+            const double a = sgm::div_r(k2.x, sk, r), b = sgm::div_r(yi, sk, r);
+            dnf = dnf + a * a;
+            dny = dny + b * b;
+            r2.x = r;
+        }
+        if (i + 1 < NX) {
+            const double yi = y2.y;
+            const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
+            const double sk = ATOL + RTOL * fabs(yi);
+            const double a = sgm::div_r(k2.y, sk, r), b = sgm::div_r(yi, sk, r);
+            dnf = dnf + a * a;
+            dny = dny + b * b;
+            r2.y = r;
+        }
+        c.set_pair(H_PE + i, r2);                            // the second half divides by the same scales
     }
     // dny / dnf through div_nr: bit-identical for these operands (both above 1e-10)
     double h = (dnf <= 1e-10 || dny <= 1e-10) ? 1.0e-6 : sqrt(sgm::div_nr(dny, dnf)) * 0.01;
@@ -356,13 +389,20 @@ __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
 template <int BLOCK>
 __device__ __noinline__ double hinit_second(double *col, double h, double dnf, double hmax)
 {
-    const Column<BLOCK> c{col, nullptr};
+    const Column<BLOCK> c{col};
     double der2 = 0.0;
-#pragma unroll 4
-    for (int i = 0; i < NX; i++) {
-        const double sk = ATOL + RTOL * fabs(c.vec(H_Y + i));
-        const double a = sgm::div_r(c.vec(H_P7 + i) - c.vec(H_K1 + i), sk, c.vec(H_PE + i));   // reciprocal left by the first half
-        der2 = der2 + a * a;
+    SG_FOR_PAIRS(i) {
+        const double2 y2 = c.pair(H_Y + i), k2 = c.pair(H_K1 + i), f2 = c.pair(H_P7 + i), r2 = c.pair(H_PE + i);
+        {
+            const double sk = ATOL + RTOL * fabs(y2.x);
+            const double a = sgm::div_r(f2.x - k2.x, sk, r2.x);   // reciprocal left by the first half
+            der2 = der2 + a * a;
+        }
+        if (i + 1 < NX) {
+            const double sk = ATOL + RTOL * fabs(y2.y);
+            const double a = sgm::div_r(f2.y - k2.y, sk, r2.y);
+            der2 = der2 + a * a;
+        }
     }
     der2 = sgm::div_nr(sqrt(der2), h);                       // h >= 1e-6
     const double der12 = fmax(fabs(der2), sqrt(dnf));
@@ -430,7 +470,8 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     if (DEFER && mode == MINUTE_IDLE) idid = 1;
     if (!DEFER || mode != MINUTE_IDLE) {
 #pragma unroll
-        for (int i = 0; i < NX; i++) { yt[i] = y[i]; c.set(H_Y + i, y[i]); }
+        for (int i = 0; i < NX; i++) yt[i] = y[i];
+        store_vec(c, H_Y, y);
     }
     if (DEFER && mode == MINUTE_RESUME) {
         h = sp->h; x = sp->x; lfacold = sp->lfacold;
@@ -441,6 +482,8 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     // The loop condition is a warp vote: lanes whose minute is complete wait here instead of running ahead
     // into the next minute on their own (without it ptxas leaves the warp split for the rest of the episode:
     // 12.8 of 32 lanes active per issued instruction, profiles/r01_i1_*).
+    // Every arm walks the states two at a time (SG_FOR_PAIRS): one 16-byte shared-memory access per vector and pair;
+    // "lo" / "hi" below are the two states of a pair, and the arithmetic per state is unchanged.
 #pragma unroll 1
     while (__any_sync(lanes, idid == 0)) {
         if (idid != 0) continue;
@@ -451,89 +494,154 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         case PH_K1: {                                        // kt = k1 = f(x, y)
             h = carry_h ? h_carry : 0.0;
             if (h == 0.0) {                                  // HINIT, first half
-#pragma unroll
-                for (int i = 0; i < NX; i++) c.set(H_K1 + i, kt[i]);
+                store_vec(c, H_K1, kt);
                 const HinitGuess g = hinit_first<BLOCK>(c.base, hmax);
                 h = g.h;
                 dnf = g.dnf;
-#pragma unroll
-                for (int i = 0; i < NX; i++) yt[i] = c(H_Y + i) + h * kt[i];
+                SG_FOR_PAIRS(i) {
+                    const double2 y2 = c.pair(H_Y + i);
+                    yt[i] = y2.x + h * kt[i];
+                    if (i + 1 < NX) yt[i + 1 < NX ? i + 1 : i] = y2.y + h * kt[i + 1 < NX ? i + 1 : i];
+                }
                 phase = PH_HINIT;
             } else {
                 begin_step = true;
             }
         } break;
         case PH_HINIT: {                                     // kt = f(x + h, y + h*k1)
-#pragma unroll
-            for (int i = 0; i < NX; i++) c.set(H_P7 + i, kt[i]);
+            store_vec(c, H_P7, kt);
             h = hinit_second<BLOCK>(c.base, h, dnf, hmax);
-#pragma unroll
-            for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
+            load_vec(c, H_K1, kt);
             begin_step = true;
         } break;
         case PH_RESUME:                                      // (the RHS of this pass is not used) k1 comes back from H_K1
-#pragma unroll
-            for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
+            load_vec(c, H_K1, kt);
             begin_step = true;
             break;
         case PH_S2:                                          // kt = k2; the sums start here from k1 (shared memory)
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                const double k1 = c(H_K1 + i);
-                yt[i] = c(H_Y + i) + h * (A31 * k1 + A32 * kt[i]);
-                P4[i] = A41 * k1 + A42 * kt[i];
-                P5[i] = A51 * k1 + A52 * kt[i];
-                P6[i] = A61 * k1 + A62 * kt[i];
+            SG_FOR_PAIRS(i) {
+                const double2 k2 = c.pair(H_K1 + i), y2 = c.pair(H_Y + i);
+                {
+                    const double k1 = k2.x;
+                    yt[i] = y2.x + h * (A31 * k1 + A32 * kt[i]);
+                    P4[i] = A41 * k1 + A42 * kt[i];
+                    P5[i] = A51 * k1 + A52 * kt[i];
+                    P6[i] = A61 * k1 + A62 * kt[i];
+                }
+                if (i + 1 < NX) {
+                    constexpr int j = 0;
+                    const int q = (i + 1 < NX ? i + 1 : i) + j;
+                    const double k1 = k2.y;
+                    yt[q] = y2.y + h * (A31 * k1 + A32 * kt[q]);
+                    P4[q] = A41 * k1 + A42 * kt[q];
+                    P5[q] = A51 * k1 + A52 * kt[q];
+                    P6[q] = A61 * k1 + A62 * kt[q];
+                }
             }
             phase = PH_S3;
             break;
         case PH_S3:                                          // kt = k3
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                const double k1 = c(H_K1 + i);
-                yt[i] = c(H_Y + i) + h * (P4[i] + A43 * kt[i]);
-                P5[i] = P5[i] + A53 * kt[i];
-                P6[i] = P6[i] + A63 * kt[i];
-                c.set(H_P7 + i, A71 * k1 + A73 * kt[i]);
-                c.set(H_PE + i, E1 * k1 + E3 * kt[i]);
+            SG_FOR_PAIRS(i) {
+                const double2 k2 = c.pair(H_K1 + i), y2 = c.pair(H_Y + i);
+                double2 p7 = make_double2(0.0, 0.0), pe = make_double2(0.0, 0.0);
+                {
+                    const double k1 = k2.x;
+                    yt[i] = y2.x + h * (P4[i] + A43 * kt[i]);
+                    P5[i] = P5[i] + A53 * kt[i];
+                    P6[i] = P6[i] + A63 * kt[i];
+                    p7.x = A71 * k1 + A73 * kt[i];
+                    pe.x = E1 * k1 + E3 * kt[i];
+                }
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    const double k1 = k2.y;
+                    yt[q] = y2.y + h * (P4[q] + A43 * kt[q]);
+                    P5[q] = P5[q] + A53 * kt[q];
+                    P6[q] = P6[q] + A63 * kt[q];
+                    p7.y = A71 * k1 + A73 * kt[q];
+                    pe.y = E1 * k1 + E3 * kt[q];
+                }
+                c.set_pair(H_P7 + i, p7);
+                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S4;
             break;
         case PH_S4:                                          // kt = k4
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                yt[i] = c(H_Y + i) + h * (P5[i] + A54 * kt[i]);
-                P6[i] = P6[i] + A64 * kt[i];
-                c.set(H_P7 + i, c(H_P7 + i) + A74 * kt[i]);
-                c.set(H_PE + i, c(H_PE + i) + E4 * kt[i]);
+            SG_FOR_PAIRS(i) {
+                const double2 y2 = c.pair(H_Y + i);
+                double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
+                {
+                    yt[i] = y2.x + h * (P5[i] + A54 * kt[i]);
+                    P6[i] = P6[i] + A64 * kt[i];
+                    p7.x = p7.x + A74 * kt[i];
+                    pe.x = pe.x + E4 * kt[i];
+                }
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    yt[q] = y2.y + h * (P5[q] + A54 * kt[q]);
+                    P6[q] = P6[q] + A64 * kt[q];
+                    p7.y = p7.y + A74 * kt[q];
+                    pe.y = pe.y + E4 * kt[q];
+                }
+                c.set_pair(H_P7 + i, p7);
+                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S5;
             break;
         case PH_S5:                                          // kt = k5
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                yt[i] = c(H_Y + i) + h * (P6[i] + A65 * kt[i]);
-                c.set(H_P7 + i, c(H_P7 + i) + A75 * kt[i]);
-                c.set(H_PE + i, c(H_PE + i) + E5 * kt[i]);
+            SG_FOR_PAIRS(i) {
+                const double2 y2 = c.pair(H_Y + i);
+                double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
+                {
+                    yt[i] = y2.x + h * (P6[i] + A65 * kt[i]);
+                    p7.x = p7.x + A75 * kt[i];
+                    pe.x = pe.x + E5 * kt[i];
+                }
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    yt[q] = y2.y + h * (P6[q] + A65 * kt[q]);
+                    p7.y = p7.y + A75 * kt[q];
+                    pe.y = pe.y + E5 * kt[q];
+                }
+                c.set_pair(H_P7 + i, p7);
+                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S6;
             break;
         case PH_S6:                                          // kt = k6; yt becomes the 5th-order solution
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                yt[i] = c(H_Y + i) + h * (c(H_P7 + i) + A76 * kt[i]);
-                c.set(H_PE + i, c(H_PE + i) + E6 * kt[i]);
+            SG_FOR_PAIRS(i) {
+                const double2 y2 = c.pair(H_Y + i), p7 = c.pair(H_P7 + i);
+                double2 pe = c.pair(H_PE + i);
+                {
+                    yt[i] = y2.x + h * (p7.x + A76 * kt[i]);
+                    pe.x = pe.x + E6 * kt[i];
+                }
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    yt[q] = y2.y + h * (p7.y + A76 * kt[q]);
+                    pe.y = pe.y + E6 * kt[q];
+                }
+                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S7;
             break;
         default: {                                           // kt = k7 = f(x + h, y1): error estimate + control
             double err = 0.0;
-#pragma unroll
-            for (int i = 0; i < NX; i++) {
-                const double e = (c(H_PE + i) + E7 * kt[i]) * h;
-                const double sk = ATOL + RTOL * sgm::max_sel(fabs(c(H_Y + i)), fabs(yt[i]));
-                const double a = sgm::div_nr(e, sk);
-                err = err + a * a;
+            SG_FOR_PAIRS(i) {
+                const double2 y2 = c.pair(H_Y + i), pe = c.pair(H_PE + i);
+                {
+                    const double e = (pe.x + E7 * kt[i]) * h;
+                    const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.x), fabs(yt[i]));
+                    const double a = sgm::div_nr(e, sk);
+                    err = err + a * a;
+                }
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    const double e = (pe.y + E7 * kt[q]) * h;
+                    const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.y), fabs(yt[q]));
+                    const double a = sgm::div_nr(e, sk);
+                    err = err + a * a;
+                }
             }
             const StepControl sc = step_control(err, lfacold, h);
             err = sc.err;
@@ -541,8 +649,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             if (err <= 1.0) {
                 lfacold = (err > 1.0e-4) ? sc.lerr : c(H_L4);        // facold = max(err, 1e-4)
                 naccpt++;
-#pragma unroll
-                for (int i = 0; i < NX; i++) c.set(H_Y + i, yt[i]);   // kt is k1 of the next step (FSAL)
+                store_vec(c, H_Y, yt);                       // kt is k1 of the next step (FSAL)
                 x = x + h;
                 if (last) {
                     idid = 1;
@@ -557,8 +664,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 reject = true;
                 if (naccpt >= 1) cnt.nrej++;
                 last = false;
-#pragma unroll
-                for (int i = 0; i < NX; i++) kt[i] = c(H_K1 + i);
+                load_vec(c, H_K1, kt);
                 begin_step = true;
             }
             h = hnew;
@@ -566,8 +672,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         }
         if (begin_step) {                                    // kt = k1 of the step that starts here
             if (DEFER && cap > 0 && nstep >= cap) {          // put the rest of this minute aside
-#pragma unroll
-                for (int i = 0; i < NX; i++) c.set(H_K1 + i, kt[i]);
+                store_vec(c, H_K1, kt);
                 sp->h = h; sp->x = x; sp->lfacold = lfacold;
                 sp->nstep = nstep; sp->naccpt = naccpt; sp->nrej = cnt.nrej; sp->reject = reject ? 1 : 0;
                 idid = IDID_SUSPENDED;
@@ -578,19 +683,18 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 if ((x + 1.01 * h - xend) > 0.0) { h = xend - x; last = true; }
                 nstep++;
                 const double ha = h * A21;
-#pragma unroll
-                for (int i = 0; i < NX; i++) {
-                    const double k = kt[i];
-                    c.set(H_K1 + i, k);
-                    yt[i] = c(H_Y + i) + ha * k;
+                store_vec(c, H_K1, kt);
+                SG_FOR_PAIRS(i) {
+                    const double2 y2 = c.pair(H_Y + i);
+                    yt[i] = y2.x + ha * kt[i];
+                    if (i + 1 < NX) yt[i + 1 < NX ? i + 1 : i] = y2.y + ha * kt[i + 1 < NX ? i + 1 : i];
                 }
                 phase = PH_S2;
             }
         }
     }
     if (DEFER && mode == MINUTE_IDLE) return 1;
-#pragma unroll
-    for (int i = 0; i < NX; i++) y[i] = c(H_Y + i);
+    load_vec(c, H_Y, y);
     if (DEFER && idid == IDID_SUSPENDED) return idid;
     if (carry_h) h_carry = h;
     cnt.nstep += nstep;

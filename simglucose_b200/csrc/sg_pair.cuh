@@ -20,7 +20,7 @@ namespace pair {
 constexpr int PL = 32;                   // episodes per block
 constexpr int PBLOCK = 64;               // threads per block: warp 0 = role G, warp 1 = role I
 constexpr int NS = 7;                    // state slots per role
-using Col = Column<PL>;
+using Col = Column<PL, false>;       // plain layout: this kernel reads its rows one value at a time
 
 // Rows of the episode's shared-memory column after the parameter rows (H_K1 is the first vector row of the
 // single-thread layout).  Vector rows: [role][slot]; role G slots = x0, x1, x2, x3, x4, x12, pad; role I = x5..x11.
@@ -96,15 +96,15 @@ struct HinitGuess2 { double h, dnf; };
 // HINIT, first half, over all 13 states in index order (rows of both roles): h = 0.01 * |y| / |k1|.
 static __device__ __noinline__ HinitGuess2 hinit_first_all(double *col, double hmax)
 {
-    const Col c{col, nullptr};
+    const Col c{col};
     double dny = 0.0, dnf = 0.0;
 #pragma unroll 1
     for (int i = 0; i < NX; i++) {
         const int r_ = state_row(i);
-        const double yi = c.vec(R_Y + r_);
+        const double yi = c(R_Y + r_);
         const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
         const double sk = ATOL + RTOL * fabs(yi);
-        const double a = sgm::div_r(c.vec(R_K1 + r_), sk, r), b = sgm::div_r(yi, sk, r);
+        const double a = sgm::div_r(c(R_K1 + r_), sk, r), b = sgm::div_r(yi, sk, r);
         dnf = dnf + a * a;
         dny = dny + b * b;
     }
@@ -116,13 +116,13 @@ static __device__ __noinline__ HinitGuess2 hinit_first_all(double *col, double h
 // HINIT, second half: second-derivative estimate from f(x + h, y + h*k1) (R_P7 rows) and k1 (R_K1 rows).
 static __device__ __noinline__ double hinit_second_all(double *col, double h, double dnf, double hmax)
 {
-    const Col c{col, nullptr};
+    const Col c{col};
     double der2 = 0.0;
 #pragma unroll 1
     for (int i = 0; i < NX; i++) {
         const int r_ = state_row(i);
-        const double sk = ATOL + RTOL * fabs(c.vec(R_Y + r_));
-        const double a = sgm::div_nr(c.vec(R_P7 + r_) - c.vec(R_K1 + r_), sk);
+        const double sk = ATOL + RTOL * fabs(c(R_Y + r_));
+        const double a = sgm::div_nr(c(R_P7 + r_) - c(R_K1 + r_), sk);
         der2 = der2 + a * a;
     }
     der2 = sqrt(der2) / h;
@@ -367,7 +367,7 @@ __device__ __forceinline__ int minute_pair(const Col &c, const Col &v, const int
 __device__ __forceinline__ void episode_pair(const EpisodeArgs &a, const int64_t e, const bool valid, const int role,
                                              const Col &c)
 {
-    const Col v{c.base + role * NS * PL, nullptr};
+    const Col v{c.base + role * NS * PL};
     double *sd = a.sd + e;
     int32_t *si = a.si + e;
     Meal meal{0.0, 0.0, 0.0, 0.0, 0};
@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(pair::PBLOCK, 8) run_pair_kernel(const Episode
     const int lane = threadIdx.x & 31, role = threadIdx.x >> 5;
     const int64_t e = (int64_t)blockIdx.x * pair::PL + lane;
     const bool valid = e < a.n;
-    const pair::Col c{smem + lane, smem + 2 * lane};
+    const pair::Col c{smem + lane};
     if (role == 0 && valid) stage_params(c, param_source(a, e));
     __syncthreads();
     pair::episode_pair(a, e, valid, role, c);
