@@ -457,7 +457,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                                              unsigned lanes, int mode = MINUTE_FRESH, int cap = 0,
                                              Suspend *sp = nullptr)
 {
-    enum { PH_K1 = 0, PH_HINIT, PH_S2, PH_S3, PH_S4, PH_S5, PH_S6, PH_S7, PH_RESUME };
+    enum { PH_K1 = 1, PH_HINIT = 2, PH_RESUME = 4, PH_S2 = 8, PH_S3 = 16, PH_S4 = 32, PH_S5 = 64, PH_S6 = 128, PH_S7 = 256 };
     double x = t0;
     const double xend = t0 + 1.0;
     const double hmax = fabs(xend - t0);
@@ -490,35 +490,10 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         rhs(c, m, yt, kt);
 
         bool begin_step = false;
-        switch (phase) {
-        case PH_K1: {                                        // kt = k1 = f(x, y)
-            h = carry_h ? h_carry : 0.0;
-            if (h == 0.0) {                                  // HINIT, first half
-                store_vec(c, H_K1, kt);
-                const HinitGuess g = hinit_first<BLOCK>(c.base, hmax);
-                h = g.h;
-                dnf = g.dnf;
-                SG_FOR_PAIRS(i) {
-                    const double2 y2 = c.pair(H_Y + i);
-                    yt[i] = y2.x + h * kt[i];
-                    if (i + 1 < NX) yt[i + 1 < NX ? i + 1 : i] = y2.y + h * kt[i + 1 < NX ? i + 1 : i];
-                }
-                phase = PH_HINIT;
-            } else {
-                begin_step = true;
-            }
-        } break;
-        case PH_HINIT: {                                     // kt = f(x + h, y + h*k1)
-            store_vec(c, H_P7, kt);
-            h = hinit_second<BLOCK>(c.base, h, dnf, hmax);
-            load_vec(c, H_K1, kt);
-            begin_step = true;
-        } break;
-        case PH_RESUME:                                      // (the RHS of this pass is not used) k1 comes back from H_K1
-            load_vec(c, H_K1, kt);
-            begin_step = true;
-            break;
-        case PH_S2:                                          // kt = k2; the sums start here from k1 (shared memory)
+        // Phase dispatch as a tree of bit tests (the phases are one-hot): a dense switch becomes a jump table, whose
+        // constant-bank load and indirect branch cost more than three predictable compares (profiles/r01_s38_*).
+        if (phase & (PH_S2 | PH_S3 | PH_S4)) {
+            if (phase & PH_S2) {                                          // kt = k2; the sums start here from k1 (shared memory)
             SG_FOR_PAIRS(i) {
                 const double2 k2 = c.pair(H_K1 + i), y2 = c.pair(H_Y + i);
                 {
@@ -539,8 +514,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 }
             }
             phase = PH_S3;
-            break;
-        case PH_S3:                                          // kt = k3
+            } else if (phase & PH_S3) {                                          // kt = k3
             SG_FOR_PAIRS(i) {
                 const double2 k2 = c.pair(H_K1 + i), y2 = c.pair(H_Y + i);
                 double2 p7 = make_double2(0.0, 0.0), pe = make_double2(0.0, 0.0);
@@ -565,8 +539,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 c.set_pair(H_PE + i, pe);
             }
             phase = PH_S4;
-            break;
-        case PH_S4:                                          // kt = k4
+            } else {                                          // kt = k4
             SG_FOR_PAIRS(i) {
                 const double2 y2 = c.pair(H_Y + i);
                 double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
@@ -587,8 +560,9 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 c.set_pair(H_PE + i, pe);
             }
             phase = PH_S5;
-            break;
-        case PH_S5:                                          // kt = k5
+            }
+        } else if (phase & (PH_S5 | PH_S6 | PH_S7)) {
+            if (phase & PH_S5) {                                          // kt = k5
             SG_FOR_PAIRS(i) {
                 const double2 y2 = c.pair(H_Y + i);
                 double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
@@ -607,8 +581,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 c.set_pair(H_PE + i, pe);
             }
             phase = PH_S6;
-            break;
-        case PH_S6:                                          // kt = k6; yt becomes the 5th-order solution
+            } else if (phase & PH_S6) {                                          // kt = k6; yt becomes the 5th-order solution
             SG_FOR_PAIRS(i) {
                 const double2 y2 = c.pair(H_Y + i), p7 = c.pair(H_P7 + i);
                 double2 pe = c.pair(H_PE + i);
@@ -624,8 +597,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 c.set_pair(H_PE + i, pe);
             }
             phase = PH_S7;
-            break;
-        default: {                                           // kt = k7 = f(x + h, y1): error estimate + control
+            } else {                                           // kt = k7 = f(x + h, y1): error estimate + control
             double err = 0.0;
             SG_FOR_PAIRS(i) {
                 const double2 y2 = c.pair(H_Y + i), pe = c.pair(H_PE + i);
@@ -668,7 +640,33 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 begin_step = true;
             }
             h = hnew;
-        } break;
+            }
+        } else {
+            if (phase & PH_K1) {                                        // kt = k1 = f(x, y)
+            h = carry_h ? h_carry : 0.0;
+            if (h == 0.0) {                                  // HINIT, first half
+                store_vec(c, H_K1, kt);
+                const HinitGuess g = hinit_first<BLOCK>(c.base, hmax);
+                h = g.h;
+                dnf = g.dnf;
+                SG_FOR_PAIRS(i) {
+                    const double2 y2 = c.pair(H_Y + i);
+                    yt[i] = y2.x + h * kt[i];
+                    if (i + 1 < NX) yt[i + 1 < NX ? i + 1 : i] = y2.y + h * kt[i + 1 < NX ? i + 1 : i];
+                }
+                phase = PH_HINIT;
+            } else {
+                begin_step = true;
+            }
+            } else if (phase & PH_HINIT) {                                     // kt = f(x + h, y + h*k1)
+            store_vec(c, H_P7, kt);
+            h = hinit_second<BLOCK>(c.base, h, dnf, hmax);
+            load_vec(c, H_K1, kt);
+            begin_step = true;
+            } else {                                      // (the RHS of this pass is not used) k1 comes back from H_K1
+            load_vec(c, H_K1, kt);
+            begin_step = true;
+            }
         }
         if (begin_step) {                                    // kt = k1 of the step that starts here
             if (DEFER && cap > 0 && nstep >= cap) {          // put the rest of this minute aside
