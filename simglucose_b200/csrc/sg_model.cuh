@@ -198,24 +198,34 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     const double Et = (x[3] > ke.x) ? ke.y * (x[3] - ke.x) : 0.0;           // :158-161
     const double egp = (0.0 > EGPt) ? 0.0 : EGPt;                           // max(EGPt, 0) :165
     const double2 k12 = c.pair(H_k1), fk = c.pair(H_Fsnc);                  // (k1, k2), (Fsnc, Km0)
-    dx[3] = mask_nonneg(x[3], egp + Rat - fk.x - Et - k12.x * x[3] + k12.y * x[4]);   // :165-167
+    dx[3] = egp + Rat - fk.x - Et - k12.x * x[3] + k12.y * x[4];            // :165-166
     const double2 vm = c.pair(H_Vm0);                                       // Vm0, Vmx
     const double Vmt = vm.x + vm.y * x[6];                                  // :169
     const double Uidt = sgm::div_nr(Vmt * x[4], fk.y + x[4]);               // :171
-    dx[4] = mask_nonneg(x[4], -Uidt + k12.x * x[3] - k12.y * x[4]);         // :172-173
+    dx[4] = -Uidt + k12.x * x[3] - k12.y * x[4];                            // :172
     const double2 am = c.pair(H_ka2), mm = c.pair(H_m24), km = c.pair(H_ka1);   // (ka2, m2), (m2+m4, m1), (ka1, m1+m30)
-    dx[5] = mask_nonneg(x[5], -mm.x * x[5] + mm.y * x[9] + km.x * x[10] + am.x * x[11]);
+    dx[5] = -mm.x * x[5] + mm.y * x[9] + km.x * x[10] + am.x * x[11];       // :176
     const double2 vi = c.pair(H_Vi);                                        // Vi, 1/Vi
     const double It = sgm::div_r(x[5], vi.x, vi.y);                         // :178
     const double2 pk = c.pair(H_p2u), ik = c.pair(H_Ib);                    // (p2u, ki), (Ib, kd)
     dx[6] = -pk.x * x[6] + pk.x * (It - ik.x);                              // :182
     dx[7] = -pk.y * (x[7] - It);                                            // :185
     dx[8] = -pk.y * (x[8] - x[7]);                                          // :187
-    dx[9] = mask_nonneg(x[9], -km.y * x[9] + am.y * x[5]);                  // :190-191
+    dx[9] = -km.y * x[9] + am.y * x[5];                                     // :190
     const double2 ak = c.pair(H_kad);                                       // ka1 + kd, ksc
-    dx[10] = mask_nonneg(x[10], m.ins - ak.x * x[10]);                      // :194-195
-    dx[11] = mask_nonneg(x[11], ik.y * x[10] - am.x * x[11]);               // :197-198
-    dx[12] = mask_nonneg(x[12], -ak.y * x[12] + ak.y * x[3]);               // :201-202
+    dx[10] = m.ins - ak.x * x[10];                                          // :194
+    dx[11] = ik.y * x[10] - am.x * x[11];                                   // :197
+    dx[12] = -ak.y * x[12] + ak.y * x[3];                                   // :201
+    // (x >= 0) * dxdt on seven states (:167,173,179,191,195,198,202).  Or-ing the sign bits and running these selects
+    // only in a warp that holds a negative state was measured in s41: 15 instructions fewer per pass and 3 % SLOWER
+    // (the vote and branch end the basic block in which the RHS tail overlaps the stage arithmetic).
+    dx[3] = mask_nonneg(x[3], dx[3]);
+    dx[4] = mask_nonneg(x[4], dx[4]);
+    dx[5] = mask_nonneg(x[5], dx[5]);
+    dx[9] = mask_nonneg(x[9], dx[9]);
+    dx[10] = mask_nonneg(x[10], dx[10]);
+    dx[11] = mask_nonneg(x[11], dx[11]);
+    dx[12] = mask_nonneg(x[12], dx[12]);
 }
 
 // InsulinPump.basal / .bolus, pump.py:23-39.  np.round == round-half-even == rint().
