@@ -178,16 +178,13 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     const double kmax = kk.x;
     const double qsto = x[0] + x[1];                                        // :126
     dx[0] = -kmax * x[0] + m.d;                                             // :133
-    double kgut;
-    if (m.fed) {                                                            // :135-142
-        // tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh)
-        const double2 ab = c.pair(H_aa), cd = c.pair(H_cc);                 // (aa, b*Dbar), (cc, d*Dbar)
-        const double tdiff = sgm::tanh_diff(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
-        const double2 kh = c.pair(H_kmin);                                  // kmin, (kmax - kmin) / 2
-        kgut = kh.x + kh.y * (tdiff + 2.0);
-    } else {
-        kgut = kmax;
-    }
+    // :135-142, branch-free: tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh),
+    // evaluated for every lane and discarded by the select when Dbar == 0
+    const double2 ab = c.pair(H_aa), cd = c.pair(H_cc);                     // (aa, b*Dbar), (cc, d*Dbar)
+    const double tdiff = sgm::tanh_diff(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
+    const double2 kh = c.pair(H_kmin);                                      // kmin, (kmax - kmin) / 2
+    const double kfed = kh.x + kh.y * (tdiff + 2.0);
+    const double kgut = m.fed ? kfed : kmax;
     dx[1] = kmax * x[0] - x[1] * kgut;                                      // :145
     dx[2] = kgut * x[1] - kk.y * x[2];                                      // :148
     const double2 fb = c.pair(H_fk), rk = c.pair(H_rBW);                    // (f*kabs, BW), (1/BW, kp1)
