@@ -495,6 +495,8 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
     while (__any_sync(lanes, idid == 0)) {
         if (idid != 0) continue;
         rhs(c, m, yt, kt);
+        double2 yy[NV / 2];                                  // y for the arm, fetched ahead of the dispatch
+        SG_FOR_PAIRS(i) yy[i / 2] = c.pair(H_Y + i);
 
         bool begin_step = false;
         // Phase dispatch as a tree of bit tests (the phases are one-hot): a dense switch becomes a jump table, whose
@@ -502,7 +504,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         if (phase & (PH_S2 | PH_S3 | PH_S4)) {
             if (phase & PH_S2) {                                          // kt = k2; the sums start here from k1 (shared memory)
             SG_FOR_PAIRS(i) {
-                const double2 k2 = c.pair(H_K1 + i), y2 = c.pair(H_Y + i);
+                const double2 k2 = c.pair(H_K1 + i), y2 = yy[i / 2];
                 {
                     const double k1 = k2.x;
                     yt[i] = y2.x + h * (A31 * k1 + A32 * kt[i]);
@@ -523,7 +525,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             phase = PH_S3;
             } else if (phase & PH_S3) {                                          // kt = k3
             SG_FOR_PAIRS(i) {
-                const double2 k2 = c.pair(H_K1 + i), y2 = c.pair(H_Y + i);
+                const double2 k2 = c.pair(H_K1 + i), y2 = yy[i / 2];
                 double2 p7 = make_double2(0.0, 0.0), pe = make_double2(0.0, 0.0);
                 {
                     const double k1 = k2.x;
@@ -548,7 +550,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             phase = PH_S4;
             } else {                                          // kt = k4
             SG_FOR_PAIRS(i) {
-                const double2 y2 = c.pair(H_Y + i);
+                const double2 y2 = yy[i / 2];
                 double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
                 {
                     yt[i] = y2.x + h * (P5[i] + A54 * kt[i]);
@@ -571,7 +573,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
         } else if (phase & (PH_S5 | PH_S6 | PH_S7)) {
             if (phase & PH_S5) {                                          // kt = k5
             SG_FOR_PAIRS(i) {
-                const double2 y2 = c.pair(H_Y + i);
+                const double2 y2 = yy[i / 2];
                 double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
                 {
                     yt[i] = y2.x + h * (P6[i] + A65 * kt[i]);
@@ -590,7 +592,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             phase = PH_S6;
             } else if (phase & PH_S6) {                                          // kt = k6; yt becomes the 5th-order solution
             SG_FOR_PAIRS(i) {
-                const double2 y2 = c.pair(H_Y + i), p7 = c.pair(H_P7 + i);
+                const double2 y2 = yy[i / 2], p7 = c.pair(H_P7 + i);
                 double2 pe = c.pair(H_PE + i);
                 {
                     yt[i] = y2.x + h * (p7.x + A76 * kt[i]);
@@ -607,7 +609,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             } else {                                           // kt = k7 = f(x + h, y1): error estimate + control
             double err = 0.0;
             SG_FOR_PAIRS(i) {
-                const double2 y2 = c.pair(H_Y + i), pe = c.pair(H_PE + i);
+                const double2 y2 = yy[i / 2], pe = c.pair(H_PE + i);
                 {
                     const double e = (pe.x + E7 * kt[i]) * h;
                     const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.x), fabs(yt[i]));
@@ -657,7 +659,7 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                 h = g.h;
                 dnf = g.dnf;
                 SG_FOR_PAIRS(i) {
-                    const double2 y2 = c.pair(H_Y + i);
+                    const double2 y2 = yy[i / 2];
                     yt[i] = y2.x + h * kt[i];
                     if (i + 1 < NX) yt[i + 1 < NX ? i + 1 : i] = y2.y + h * kt[i + 1 < NX ? i + 1 : i];
                 }
