@@ -150,11 +150,77 @@ void run_coissue(const char *name, double *out)
     printf("co-issue %-28s: %.3f ms, %.2f cycles per DFMA per SMSP\n", name, ms, ms * 1e-3 * 1.965e9 / dfma_per_smsp);
 }
 
-int main()
+// ---- 4. instruction supply --------------------------------------------------------------------------------
+// Straight-line body of N independent instructions (8 accumulator chains, so no dependency waits): MIX 0 = FFMA only
+// (issue limit 1 per cycle), MIX 1 = DFMA and FFMA alternating (FP64 pipe half busy, as in run_kernel).  Blocks of
+// 128 threads = one warp per scheduler; with a body larger than the per-scheduler instruction buffer every 128-byte
+// line (8 instructions) has to come from the SM's instruction cache.
+template <int N, int MIX>
+__global__ void __launch_bounds__(128) supply_kernel(double *out, long long *cyc, int iters, float a, float b, int skew)
+{
+    float v[8];
+    double d[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { v[i] = a + i + threadIdx.x; d[i] = v[i]; }
+    const int w = (threadIdx.x >> 5) + 4 * (blockIdx.x & 1);
+    for (int s = 0; s < w * skew; s++) v[0] = fmaf(v[0], a, b);
+    const double da = a, db = b;
+    long long t0 = clock64();
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < N / 8; r++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (MIX == 1 && (i & 1)) d[i] = fma(d[i], da, db);
+                else v[i] = fmaf(v[i], a, b);
+            }
+        }
+    }
+    long long t1 = clock64();
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += v[i] + d[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
+}
+
+template <int N, int MIX>
+void run_supply(double *out, long long *cyc, int blocks_per_sm)
+{
+    const int iters = (1 << 22) / N;
+    for (int skew = 0; skew <= 997; skew += 997) {
+        supply_kernel<N, MIX><<<148 * blocks_per_sm, 128>>>(out, cyc, iters, 1.0000001f, 1e-9f, skew);
+        CK(cudaDeviceSynchronize());
+        cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEventRecord(e0);
+        supply_kernel<N, MIX><<<148 * blocks_per_sm, 128>>>(out, cyc, iters, 1.0000001f, 1e-9f, skew);
+        cudaEventRecord(e1);
+        CK(cudaDeviceSynchronize());
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        const double per_warp = (double)iters * N;
+        printf("%s body %3d KB  warps/SMSP %d  skew %3d: %.3f ms, %.2f cycles per instruction per warp, %.1f per 128-byte line\n",
+               MIX ? "DFMA+FFMA" : "FFMA     ", N * 16 / 1024, blocks_per_sm, skew, ms, ms * 1e-3 * 1.965e9 / per_warp,
+               8 * ms * 1e-3 * 1.965e9 / per_warp);
+    }
+}
+
+int main(int argc, char **argv)
 {
     double *out; long long *cyc;
     CK(cudaMalloc(&out, sizeof(double) * 148 * 8 * 1024));
     CK(cudaMalloc(&cyc, 8));
+    if (argc > 1 && argv[1][0] == '4') {
+        printf("== 4. instruction supply: straight-line independent instructions, 128-thread blocks ==\n");
+        for (int bps = 1; bps <= 3; bps++) {
+            run_supply<128, 0>(out, cyc, bps);
+            run_supply<512, 0>(out, cyc, bps);
+            run_supply<1536, 0>(out, cyc, bps);
+            run_supply<128, 1>(out, cyc, bps);
+            run_supply<512, 1>(out, cyc, bps);
+            run_supply<1536, 1>(out, cyc, bps);
+        }
+        return 0;
+    }
     printf("== 1. FP64 latency / throughput (clock64 on one warp; all SMs busy) ==\n");
     run_chain<1, 0>("DFMA", 32, out, cyc);
     run_chain<1, 1>("DADD", 32, out, cyc);
