@@ -478,7 +478,7 @@ __global__ void __launch_bounds__(256) risk_window_kernel(const ElementwiseArgs 
     __shared__ double part[256][4];
     double sl = 0.0, sh = 0.0, nl = 0.0, nh = 0.0;
     for (int64_t i = threadIdx.x; i < a.n; i += 256) {
-        const double f = 1.509 * (pow(log(a.in[i]), 1.084) - 5.381);
+        const double f = risk_f(a.in[i]);
         if (f < 0.0) { sl += 10.0 * (f * f); nl += 1.0; }
         if (f > 0.0) { sh += 10.0 * (f * f); nh += 1.0; }
     }

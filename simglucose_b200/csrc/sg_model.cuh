@@ -236,10 +236,23 @@ __device__ __forceinline__ double pump_quantise(double amount, double vmin, doub
     return v;
 }
 
-// risk_index([BG], 1), risk.py:5-17 (NaN -> 0 via nan_to_num; BG < 1 gives log < 0 -> pow NaN).
+// f(BG) = 1.509 * (ln(BG)^1.084 - 5.381), risk.py:9-10.  log and pow come from sg_math.cuh (the code the step-size
+// controller already keeps in the instruction cache; CUDA's pow is ~180 instructions per inlined call and the episode
+// kernels evaluate the risk two or three times per env-step) and the function is not inlined.  NaN, negative BG and
+// BG < 1 (log < 0 -> pow NaN) return NaN; BG == 1 gives 0^1.084 = 0; +inf stays +inf.
+static __device__ __noinline__ double risk_f(double bg)
+{
+    if (!(bg >= 1.0)) return __longlong_as_double(0x7ff8000000000000ll);
+    if (bg > DBL_MAX) return bg;
+    const double lg = sgm::log_core(bg);
+    const double pw = (lg > 0.0) ? sgm::exp_core(1.084 * sgm::log_core(lg)) : 0.0;
+    return 1.509 * (pw - 5.381);
+}
+
+// risk_index([BG], 1), risk.py:5-17 (NaN -> 0 via nan_to_num; +inf -> DBL_MAX).
 __device__ __forceinline__ void risk_index(double bg, double &lbgi, double &hbgi, double &ri)
 {
-    const double f = 1.509 * (pow(log(bg), 1.084) - 5.381);
+    const double f = risk_f(bg);
     lbgi = (f < 0.0) ? 10.0 * (f * f) : 0.0;
     hbgi = (f > 0.0) ? 10.0 * (f * f) : 0.0;
     if (isinf(lbgi)) lbgi = DBL_MAX;
