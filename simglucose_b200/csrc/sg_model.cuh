@@ -136,8 +136,8 @@ __device__ __forceinline__ Minute minute_setup_rate(const Column<BLOCK> &c, doub
     // (same inputs, same results -- the cache cannot change a bit)
     if (m.fed && Dbar != c(H_Dbar)) {                       // t1dpatient.py:136-140
         c.set(H_Dbar, Dbar);
-        c.set(H_aa, 5.0 / 2.0 / (1.0 - c(H_b)) / Dbar);
-        c.set(H_cc, 5.0 / 2.0 / c(H_d) / Dbar);
+        c.set(H_aa, sgm::div_ieee(sgm::div_ieee(5.0 / 2.0, 1.0 - c(H_b)), Dbar));
+        c.set(H_cc, sgm::div_ieee(sgm::div_ieee(5.0 / 2.0, c(H_d)), Dbar));
         c.set(H_bD, c(H_b) * Dbar);
         c.set(H_dD, c(H_d) * Dbar);
     }
@@ -229,8 +229,8 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
 __device__ __forceinline__ double pump_quantise(double amount, double vmin, double vmax, double inc)
 {
     double v = amount * 6000.0;
-    v = rint(v / inc) * inc;
-    v = v / 6000.0;
+    v = rint(sgm::div_ieee(v, inc)) * inc;
+    v = sgm::div_ieee(v, 6000.0);
     v = (vmax < v) ? vmax : v;     // Python min(v, vmax)
     v = (vmin > v) ? vmin : v;     // Python max(v, vmin)
     return v;
