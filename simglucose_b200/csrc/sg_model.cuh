@@ -440,7 +440,7 @@ struct StepControl { double err, hnew_accept, hnew_reject, lerr; };
 
 // Step-size controller of DOPCOR (Lund stabilisation, beta = 0.04) from the summed squared scaled errors.
 // lfacold: log of facold (log_pos).  Returns the log of err as well: the caller keeps it as the next lfacold.
-static __device__ __noinline__ StepControl step_control(double errsum, double lfacold, double h)
+static __device__ __forceinline__ StepControl step_control(double errsum, double lfacold, double h)
 {
     const double beta = 0.04, safe = 0.9;
     const double expo1 = 0.2 - beta * 0.75;
