@@ -245,7 +245,7 @@ static __device__ __noinline__ double risk_f(double bg)
     if (!(bg >= 1.0)) return __longlong_as_double(0x7ff8000000000000ll);
     if (bg > DBL_MAX) return bg;
     const double lg = sgm::log_core(bg);
-    const double pw = (lg > 0.0) ? sgm::exp_core(1.084 * sgm::log_core(lg)) : 0.0;
+    const double pw = (lg > 0.0) ? sgm::pow_pos(lg, 1.084) : 0.0;          // the subroutine HINIT already uses
     return 1.509 * (pw - 5.381);
 }
 
