@@ -239,10 +239,12 @@ __device__ __forceinline__ double pump_quantise(double amount, double vmin, doub
 // f(BG) = 1.509 * (ln(BG)^1.084 - 5.381), risk.py:9-10.  log and pow come from sg_math.cuh (the code the step-size
 // controller already keeps in the instruction cache; CUDA's pow is ~180 instructions per inlined call and the episode
 // kernels evaluate the risk two or three times per env-step) and the function is not inlined.  NaN, negative BG and
-// BG < 1 (log < 0 -> pow NaN) return NaN; BG == 1 gives 0^1.084 = 0; +inf stays +inf.
+// 0 < BG < 1 (log < 0 -> pow NaN) return NaN; BG == 0 gives (-inf)^1.084 = +inf; BG == 1 gives 0^1.084 = 0; +inf stays
+// +inf (tests/test_gpu_math.py checks these against the oracle's libm evaluation).
 static __device__ __noinline__ double risk_f(double bg)
 {
-    if (!(bg >= 1.0)) return __longlong_as_double(0x7ff8000000000000ll);
+    if (!(bg >= 1.0))                                  // log(+-0) = -inf and pow(-inf, 1.084) = +inf, as in libm / numpy
+        return __longlong_as_double(bg == 0.0 ? 0x7ff0000000000000ll : 0x7ff8000000000000ll);
     if (bg > DBL_MAX) return bg;
     const double lg = sgm::log_core(bg);
     const double pw = (lg > 0.0) ? sgm::pow_pos(lg, 1.084) : 0.0;          // the subroutine HINIT already uses

@@ -78,3 +78,28 @@ def test_pow_pos_step_controller_exponents():
     # clamps: 0 and inf behave like any value beyond the controller's limits (facc1 = 5, facc2 = 0.1)
     edge = _probe(4, np.array([0.0, np.inf]), np.array([0.17, 0.17]))
     assert edge[0] < 1e-3 and edge[1] > 1e3
+
+
+def test_risk_index_against_oracle_over_the_whole_range_and_edge_cases():
+    """risk.py:5-17 through sg_risk_index (the function the episode kernels call, sg_model.cuh risk_f: in-tree log /
+    exp instead of CUDA's pow) against the oracle's libm evaluation: 1e-12 relative over BG 1..1e6 mg/dL -- the slope
+    of 10 f^2 around f = 0 (BG 112.5) amplifies one ulp of pow to ~1e-14 absolute -- and exactly the reference's
+    nan_to_num results for BG < 1, BG == 1, zero (log -> -inf, pow -> +inf: HBGI = DBL_MAX), negative, NaN and +inf."""
+    import torch
+    from helpers import O
+    from simglucose_b200 import ops
+    rng = np.random.default_rng(7)
+    bg = np.concatenate([np.exp(rng.uniform(0.0, np.log(1e6), 20000)), np.linspace(100.0, 125.0, 5001),
+                         [1.0, np.nextafter(1.0, 2.0), 1.0000001, 39.0, 600.0, 1e300, 1.7e308]])
+    out = [t.cpu().numpy() for t in ops.risk_index_elementwise(torch.from_numpy(bg).cuda())]
+    ref = np.array([O.risk(v) for v in bg]).T
+    for got, want in zip(out, ref):
+        assert np.all(np.abs(got - want) <= 1e-12 * np.maximum(np.abs(want), 1.0) + 1e-13)
+    edge = np.array([0.5, 0.999999, 0.0, -0.0, -3.5e-12, -100.0, np.nan, np.inf, 1.0])
+    out = [t.cpu().numpy() for t in ops.risk_index_elementwise(torch.from_numpy(edge).cuda())]
+    ref = np.array([O.risk(v) for v in edge]).T
+    for got, want in zip(out, ref):
+        assert np.array_equal(got[:8], want[:8])                  # zeros, and DBL_MAX for BG == +-0 and +inf
+        assert abs(got[8] - want[8]) <= 1e-12 * max(abs(want[8]), 1.0)
+    big = np.finfo(float).max
+    assert out[0][8] > 650.0 and out[1][2] == big and out[1][3] == big and out[1][7] == big    # BG == 1; +-0; +inf
