@@ -329,8 +329,14 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
     except Exception:
         pass
+    # DRAM bytes of one run_kernel launch from the committed ncu capture (profiles/r01_s60_run_kernel_dram_traffic.csv:
+    # dram__bytes_read.sum + dram__bytes_write.sum = 3,264,205,824 + 96,096,000 on the default workload -- 0.996 of the
+    # algorithmic bytes below; the traffic does not depend on the arithmetic mode).  Other workloads: not captured.
+    default_workload = (args.groups == 8840 and args.days == 3)
+    traffic = 3264205824 + 96096000 if default_workload else None
     roofline = {'bound': 'fp64', 'achieved': ach_tf, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': ach_tf / peak_tf,
-                'traffic': None, 'kernel': 'run_kernel', 'kernel_ms': kern_ms,
+                'traffic': traffic, 'traffic_unit': 'bytes per launch (ncu, session s60)' if traffic else None,
+                'kernel': 'run_kernel', 'kernel_ms': kern_ms,
                 'peak_source': 'DFMA chain probe timed in this run (sg_probe_dfma); MEASURED_PEAKS.json has no FP64 entry',
                 'algorithmic_flops_per_launch': fl, 'dopri_steps_per_minute': float(a[14] / (E * n_min)),
                 'hbm': {'achieved_gbs': hbm_bytes / (kern_ms * 1e-3) / 1e9, 'peak_gbs': peaks.get('hbm_gbs', 6650.0),
