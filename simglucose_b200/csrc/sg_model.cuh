@@ -120,6 +120,7 @@ struct Minute {
     double d;      // action.CHO * 1000                      t1dpatient.py:121
     double ins;    // action.insulin * 6000 / BW             t1dpatient.py:122
     bool fed;      // Dbar > 0                               t1dpatient.py:130,135
+    double2 ab, cd;  // (aa, b*Dbar), (cc, d*Dbar) of the gastric-emptying law: the head of the RHS's longest chain, in registers
 };
 
 // ins_per_kg: action.insulin * 6000 / BW (constant over an env-step: the caller divides once).
@@ -141,6 +142,7 @@ __device__ __forceinline__ Minute minute_setup_rate(const Column<BLOCK> &c, doub
         c.set(H_bD, c(H_b) * Dbar);
         c.set(H_dD, c(H_d) * Dbar);
     }
+    m.ab = c.pair(H_aa); m.cd = c.pair(H_cc);
     return m;
 }
 
@@ -159,6 +161,7 @@ __device__ __forceinline__ Minute minute_setup(const Column<BLOCK> &c, double ch
         c.set(H_bD, c(H_b) * Dbar);
         c.set(H_dD, c(H_d) * Dbar);
     }
+    m.ab = c.pair(H_aa); m.cd = c.pair(H_cc);
     return m;
 }
 
@@ -180,7 +183,7 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     dx[0] = -kmax * x[0] + m.d;                                             // :133
     // :135-142, branch-free: tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh),
     // evaluated for every lane and discarded by the select when Dbar == 0
-    const double2 ab = c.pair(H_aa), cd = c.pair(H_cc);                     // (aa, b*Dbar), (cc, d*Dbar)
+    const double2 ab = m.ab, cd = m.cd;                                     // (aa, b*Dbar), (cc, d*Dbar)
     const double tdiff = sgm::tanh_diff(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
     const double2 kh = c.pair(H_kmin);                                      // kmin, (kmax - kmin) / 2
     const double kfed = kh.x + kh.y * (tdiff + 2.0);
