@@ -44,22 +44,26 @@ typedef enum { SG_OK = 0, SG_ERR_ARG = -1, SG_ERR_CUDA = -2, SG_ERR_STATE = -3, 
 #define SG_FLAG_CARRY_H 1u   /* scipy 1.6.3 (Pipfile.lock) behaviour: the step size proposed at the end of one
                                 minute starts the next (WORK(7)=H); default 0 = scipy >= 1.7: HINIT every minute */
 #define SG_FLAG_FMA     2u   /* allow FMA contraction in the kernels (faster; not decision-identical to scipy) */
-#define SG_FLAG_PAIR    4u   /* sg_run / sg_step launch the warp-pair kernel: two threads (glucose side, insulin
-                                side) per episode.  Same arithmetic per state, bit-identical results in strict
-                                mode; ignored while sg_set_step_cap is active.  The environment variable
-                                SG_PAIR=0/1 overrides the flag at sg_create (A/B measurements). */
+/* 4u was SG_FLAG_PAIR (two threads per episode; measured 0.80x and removed in round 2): rejected */
 
 #define SG_FLAG_FP32    8u   /* optional single-precision mode: the patient ODE and its DOPRI5 integration run in FP32
                                 (local time, uround 1.2e-7, rtol 1e-4, FMA); pump, sensor, meal machine, risk and
                                 statistics stay FP64.  Looser bound: max |dBG| / max(|BG|, 1) <= 1e-3 over a day against
-                                the FP64 path (tests/test_gpu_fp32.py; measured 1.2e-4).  Not the graded mode; ignored while a step cap is set. */
+                                the FP64 path (tests/test_gpu_fp32.py; measured 1.2e-4).  Not the graded mode; sg_set_step_cap refuses it. */
 
 /* Controller fused into sg_run. */
 typedef enum {
     SG_CTRL_ACTIONS = 0,     /* per-step (basal, bolus) supplied by the caller: any Controller.policy
                                 (controller/base.py:11-34) evaluated outside */
-    SG_CTRL_BB = 1,          /* BBController._bb_policy, controller/basal_bolus_ctrller.py:64-80; ctrl = target, CR, CF */
-    SG_CTRL_PID = 2          /* PIDController.policy, controller/pid_ctrller.py:17-36; ctrl = P, I, D, target */
+    SG_CTRL_BB = 1,          /* BBController._bb_policy, controller/basal_bolus_ctrller.py:64-80; ctrl = target, CR, CF,
+                                basal.  basal (U/min) is u2ss * BW / 6000 of the CSV row the reference looks up by
+                                patient NAME (basal_bolus_ctrller.py:52-64); 0 = take it from the episode's own
+                                parameter row (identical for unperturbed cohort rows) */
+    SG_CTRL_PID = 2,         /* PIDController.policy, controller/pid_ctrller.py:17-36; ctrl = P, I, D, target */
+    SG_CTRL_RANDOM = 3       /* Action(basal ~ U(lo, hi), bolus 0): what gym's action_space.sample() feeds
+                                T1DSimEnv._step (envs/simglucose_gym_env.py:41-46, 78-81), drawn inside the kernel from
+                                Philox keyed by (seed, global episode index, env-step index);
+                                ctrl = lo, hi, seed, global index of episode 0 (whole numbers below 2^53) */
 } sg_controller;
 #define SG_NCTRL 4
 
@@ -148,6 +152,28 @@ int sg_rebind_streams(sg_handle h, const int32_t *meal_minute, const double *mea
  * multi-step runs are faster with cap = 0. */
 int sg_set_step_cap(sg_handle h, int32_t cap);
 
+/* Schedule-coherent launch order for the same kind of population (the other answer to the same divergence, and the
+ * one that also pays for fused multi-step runs): every `segment_steps` env-steps the episodes are counting-sorted by
+ * the minute of their next meal event (episodes in the middle of a meal: by the minutes of eating left) and the
+ * grams, and thread i of the following launches owns episode perm[i] -- the lanes of a warp then meet the meal onset,
+ * the end of the meal and the bolus edges in the same minutes.  Only the thread -> episode mapping moves; every array
+ * stays indexed by the episode and per-episode results are bit-identical to segment_steps = 0 (default, off).
+ * sg_run is cut into one launch per segment (plus three small sort launches); sg_step re-sorts every segment_steps calls.
+ * The scratch (8 B per episode of capacity + the histogram) is allocated here.  segment_steps * sample_time <= 4096. */
+int sg_set_coherence(sg_handle h, int32_t segment_steps);
+/* The current launch order perm_out [E] (a permutation of 0..E-1); SG_ERR_STATE before the first sorted launch. */
+int sg_get_launch_order(sg_handle h, int32_t *perm_out, void *stream);
+
+/* T1DSimEnv.reset for SOME episodes of a running population: the gym wrapper's reset on `done`
+ * (envs/simglucose_gym_env.py:48-51 builds a new env and resets it), batched.  mask [E] int32: non-zero = reset this
+ * episode (state, meal machine, controller state, statistics, stream positions back to 0, two noise samples
+ * consumed); the others are untouched.  The caller has already overwritten the masked COLUMNS of the bound noise /
+ * meal buffers (and x0 [SG_NX][E] if given; NULL = table x0) with the new episode's streams, e.g. with the keyed
+ * generators below.  row0 [SG_NTRACE][E] (may be NULL) receives history row 0 of the masked episodes only.
+ * From here on episodes have stream positions of their own: the host-side length check of sg_step / sg_run is
+ * replaced by the kernel's own guard, which marks an episode that runs past its noise stream with status -5. */
+int sg_reset_masked(sg_handle h, const int32_t *mask, const double *x0, double *row0, void *stream);
+
 /* patient.t at reset: T1DPatient(..., t0=...) (patient/t1dpatient.py:27,277).  Default 0. */
 int sg_set_t0(sg_handle h, int32_t t0);
 
@@ -227,7 +253,8 @@ int sg_set_episode_state(sg_handle h, const double *d_in, const int32_t *i_in, i
 int sg_get_state(sg_handle h, double *x_out /* [SG_NX][E] */, void *stream);
 int sg_get_stats(sg_handle h, double *stats_out /* [SG_NSTAT][E] */, void *stream);
 /* Per-episode solver status: 1 ok, -2 (more than 500 steps), -3 (step size too small): scipy's idid,
- * checked by the reference through _odesolver.successful() (t1dpatient.py:112-116). */
+ * checked by the reference through _odesolver.successful() (t1dpatient.py:112-116); -5: the episode needed a CGM
+ * noise sample beyond the bound stream (zero noise was used from there on). */
 int sg_get_status(sg_handle h, int32_t *status_out /* [E] */, void *stream);
 
 /* Population aggregate of the per-episode statistics, reduced with warp shuffles then a fixed-order
@@ -254,6 +281,27 @@ int sg_gen_noise(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsamp
 int sg_gen_scenarios(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
                      int32_t start_minute, int32_t horizon_minutes, uint64_t seed, int64_t episode_offset,
                      int64_t group_size, void *stream);
+
+/* Keyed variants for vector environments, whose episodes restart one by one (gym reset on `done`): key [E] int64
+ * names the Philox stream of each episode (e.g. env index + num_envs * episodes started in that slot) instead of its
+ * position, only the columns with mask[e] != 0 are written (mask NULL = all), and the scenario start is per episode
+ * (start_minute [E], minute of day). */
+int sg_gen_noise_keyed(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsample, const double *W_dev,
+                       const double *model_host, uint64_t seed, const int64_t *key, const int32_t *mask, void *stream);
+int sg_gen_scenarios_keyed(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
+                           const int32_t *start_minute, int32_t horizon_minutes, uint64_t seed, const int64_t *key,
+                           const int32_t *mask, void *stream);
+
+/* Where and how an episode starts, as the gym wrapper draws it (envs/simglucose_gym_env.py:58-73):
+ *   start_minute [E] (may be NULL)  60 * randint(0, 24)
+ *   x0 [SG_NX][E]    (may be NULL)  T1DPatient.reset with random_init_bg=True (patient/t1dpatient.py:256-270): the table
+ *                    state of patient_row[e] with x[3], x[4], x[12] ~ N(mean, 0.1 * mean), independent; n_draws
+ *                    successive randomisations, each around the one before with the same deviates (the wrapper resets
+ *                    the patient twice: n_draws = 2; 0 = the table state)
+ * Distribution-compatible (Philox); the host replay for given gym seeds is streams.random_init_state / np_random. */
+int sg_gen_episode_starts(int32_t *start_minute, double *x0, const double *table_x0_dev, const int32_t *patient_row,
+                          int64_t n_episodes, int32_t n_draws, uint64_t seed, const int64_t *key, const int32_t *mask,
+                          void *stream);
 
 /* Perturbed population (BASELINE.json configs[3]): params_soa[i][e] = table[row[e]][i] * (1 + amplitude*u),
  * u ~ U(-1, 1) i.i.d. per parameter.  table_dev: [n_rows][SG_NPARAM] on the device. */

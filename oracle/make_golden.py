@@ -206,8 +206,41 @@ def g_report(pool):
     print('wrote', os.path.normpath(path), '%.1f KB' % (os.path.getsize(path) / 1024.0), flush=True)
 
 
+def _days(job):
+    """n day schedules drawn by the reference's RandomScenario.create_scenario (scenario_gen.py:33-60) from one
+    RandomState(seed): per slot (identified by its time window) the meal minute and grams, -1 where no meal."""
+    seed, n = job
+    H._activate()
+    from datetime import datetime
+    from simglucose.simulation.scenario_gen import RandomScenario
+    sc = RandomScenario(start_time=datetime(2018, 1, 1, 0, 0, 0), seed=seed)
+    ub = np.array([9, 10, 14, 16, 20, 23]) * 60
+    t_out = np.full((n, 6), -1, dtype=np.int16)
+    g_out = np.full((n, 6), -1, dtype=np.int16)
+    for d in range(n):
+        day = sc.create_scenario()
+        for t, g in zip(day['meal']['time'], day['meal']['amount']):
+            k = int(np.searchsorted(ub, t, side='left'))
+            if t_out[d, k] < 0:                          # a second meal in the same window can only come from a shared
+                t_out[d, k] = int(t); g_out[d, k] = int(g)   # boundary minute; keep the first
+    return t_out, g_out
+
+
+def g_generator_samples(pool):
+    """Large samples of the reference's own stochastic generators, for the distribution tests of the device (Philox)
+    generators (tests/test_gpu_generators.py): 24,000 day schedules of RandomScenario."""
+    jobs = [(900 + k, 1500) for k in range(16)]
+    res = pool.map(_days, jobs)
+    out = dict(day_minute=np.concatenate([r[0] for r in res]), day_grams=np.concatenate([r[1] for r in res]),
+               day_seeds=np.array([j[0] for j in jobs], dtype=np.int32))
+    path = os.path.join(OUT, 'generator_samples.npz')
+    np.savez_compressed(path, **out)
+    print('wrote', os.path.normpath(path), '%.1f KB' % (os.path.getsize(path) / 1024.0), flush=True)
+
+
 GROUPS = dict(golden_config=g_golden_config, custom=g_custom, cohort_bb=g_cohort_bb, cohort_pid=g_cohort_pid,
-              open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise, report=g_report)
+              open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise, report=g_report,
+              generator_samples=g_generator_samples)
 
 if __name__ == '__main__':
     groups = sys.argv[1:] or list(GROUPS)

@@ -24,17 +24,20 @@ PARAMS = ['BW', 'u2ss', 'kmax', 'kmin', 'b', 'd', 'kabs', 'f', 'kp1', 'kp2', 'kp
 TRACE_COLS = ['BG', 'CGM', 'CHO', 'insulin', 'LBGI', 'HBGI', 'Risk', 'obs', 'reward', 'done', 'basal', 'bolus']
 STAT_COLS = ['rows', 'sum_bg', 'min_bg', 'max_bg', 'sum_lbgi', 'sum_hbgi', 'sum_risk', 'sum_reward', 'lt50',
              'lt70', 'inrange', 'gt180', 'gt250', 'first_done', 'dopri_steps', 'dopri_rejects']
-CTRL_ACTIONS, CTRL_BB, CTRL_PID = 0, 1, 2
-FLAG_CARRY_H, FLAG_FMA, FLAG_PAIR, FLAG_FP32 = 1, 2, 4, 8
+CTRL_ACTIONS, CTRL_BB, CTRL_PID, CTRL_RANDOM = 0, 1, 2, 3
+FLAG_CARRY_H, FLAG_FMA, FLAG_FP32 = 1, 2, 8
+STATUS_STREAM_EXHAUSTED = -5
 
 # every symbol include/simglucose_b200.h declares
 SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_hardware', 'sg_load_params',
            'sg_reset', 'sg_step', 'sg_run', 'sg_get_state', 'sg_get_stats', 'sg_get_status',
            'sg_reduce_stats', 'sg_num_episodes', 'sg_launch_count',
-           'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_set_step_cap', 'sg_patient_step', 'sg_model', 'sg_pump',
+           'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_set_step_cap', 'sg_set_coherence', 'sg_get_launch_order',
+           'sg_reset_masked', 'sg_patient_step', 'sg_model', 'sg_pump',
            'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
            'sg_report_stats', 'sg_cvga_zones',
-           'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma']
+           'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma',
+           'sg_gen_noise_keyed', 'sg_gen_scenarios_keyed', 'sg_gen_episode_starts']
 
 
 class Hardware(C.Structure):
@@ -72,6 +75,9 @@ def load():
     L.sg_rebind_streams.argtypes = [vp, ip, dp, C.c_int32, dp, C.c_int64]
     L.sg_set_t0.argtypes = [vp, C.c_int32]
     L.sg_set_step_cap.argtypes = [vp, C.c_int32]
+    L.sg_set_coherence.argtypes = [vp, C.c_int32]
+    L.sg_get_launch_order.argtypes = [vp, ip, vp]
+    L.sg_reset_masked.argtypes = [vp, ip, dp, dp, vp]
     L.sg_patient_step.argtypes = [vp, dp, dp, dp, vp]
     L.sg_model.argtypes = [vp, C.c_int64, dp, dp, dp, dp, dp, ip, dp, dp, vp]
     L.sg_pump.argtypes = [dp, dp, C.c_int64, C.c_double, C.c_double, C.c_double, vp]
@@ -97,6 +103,9 @@ def load():
         L.sg_gen_perturbed_params.argtypes = [dp, dp, ip, C.c_int64, C.c_double, C.c_uint64, C.c_int64, vp]
         L.sg_probe_dfma.argtypes = [dp, C.c_int32, C.c_int32, C.c_int64, vp]
         L.sg_gen_uniform.argtypes = [dp, C.c_int64, C.c_double, C.c_double, C.c_uint64, C.c_uint64, vp]
+        L.sg_gen_noise_keyed.argtypes = [dp, C.c_int64, C.c_int64, C.c_int32, dp, C.POINTER(C.c_double), C.c_uint64, ip, ip, vp]
+        L.sg_gen_scenarios_keyed.argtypes = [ip, dp, C.c_int64, C.c_int32, ip, C.c_int32, C.c_uint64, ip, ip, vp]
+        L.sg_gen_episode_starts.argtypes = [ip, dp, dp, ip, C.c_int64, C.c_int32, C.c_uint64, ip, ip, vp]
     for name in SYMBOLS:
         f = getattr(L, name, None)
         if f is not None and f.restype is C.c_int and name != 'sg_version':

@@ -26,6 +26,7 @@ UNITS = [
     ('sg_kernels_strict.o', 'sg_kernels.cu', ['-fmad=false', '-DSG_NS=sg_strict']),
     ('sg_kernels_fma.o', 'sg_kernels.cu', ['-fmad=true', '-DSG_NS=sg_fma', '-DSG_WITH_FP32']),
     ('sg_generators.o', 'sg_generators.cu', ['-fmad=true']),
+    ('sg_coherence.o', 'sg_coherence.cu', ['-fmad=false']),
     ('sg_report.o', 'sg_report.cu', ['-fmad=false']),
     ('sg_capi.o', 'sg_capi.cu', ['-fmad=false']),
 ]

@@ -27,10 +27,12 @@ class BBController(Controller):
         return rec['u2ss'], rec['BW'], q['CR'], q['CF']
 
     def device_spec(self, name):
-        """('bb', (target, CR, CF)) when the kernel's BB policy applies to this patient name, else None."""
+        """('bb', (target, CR, CF, basal)) when the kernel's BB policy applies to this patient name, else None.
+        basal = u2ss * BW / 6000 of the CSV row found by NAME, as _bb_policy computes it -- not of the parameter
+        Series the patient object may carry (a user-modified row keeps the cohort basal, as in the reference)."""
         if isinstance(name, str) and P.quest_record(name) is not None:
-            q = P.quest_record(name)
-            return 'bb', (float(self.target), float(q['CR']), float(q['CF']), 0.0)
+            u2ss, BW, CR, CF = self._lookup(name)
+            return 'bb', (float(self.target), float(CR), float(CF), float(u2ss * BW / 6000))
         return None
 
     def policy(self, observation, reward, done, **kwargs):

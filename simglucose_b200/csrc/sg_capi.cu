@@ -58,6 +58,15 @@ struct sg_context {
     int32_t step_cap = 0;
     double *defer_d = nullptr;
     int32_t *defer_i = nullptr, *defer_list = nullptr, *defer_count = nullptr;
+    // schedule-coherent launch order (sg_set_coherence)
+    int32_t coherence_steps = 0;       // env-steps between two sorts; 0 = episodes run in index order
+    int32_t steps_since_sort = 0;
+    bool perm_valid = false;
+    int32_t *perm = nullptr, *sort_keys = nullptr, *sort_hist = nullptr;
+    int32_t sort_n_keys = 0;
+    // episodes with positions of their own (sg_reset_masked): the host-side stream length check no longer applies
+    bool per_episode_positions = false;
+    int64_t steps_total = 0;           // env-steps launched since sg_create (Philox counter of SG_CTRL_RANDOM)
 };
 
 namespace {
@@ -85,6 +94,7 @@ sgk::EpisodeArgs base_args(const sg_context *h)
     a.hw = h->hw;
     a.carry_h = (h->flags & SG_FLAG_CARRY_H) ? 1 : 0;
     a.step_cap = h->step_cap;
+    a.perm = (h->coherence_steps > 0 && h->perm_valid) ? h->perm : nullptr;
     a.defer_d = h->defer_d; a.defer_i = h->defer_i; a.defer_list = h->defer_list; a.defer_count = h->defer_count;
     return a;
 }
@@ -110,7 +120,10 @@ int sg_create(int device, int64_t capacity, uint32_t flags, sg_handle *out)
     if (!g.ok) return fail(SG_ERR_CUDA, "sg_create: cudaSetDevice failed");
     sg_context *h = new (std::nothrow) sg_context();
     if (!h) return fail(SG_ERR_NOMEM, "sg_create: host allocation failed");
-    if (const char *ev = getenv("SG_PAIR")) flags = (ev[0] == '1') ? (flags | SG_FLAG_PAIR) : (flags & ~SG_FLAG_PAIR);
+    if (flags & ~(SG_FLAG_CARRY_H | SG_FLAG_FMA | SG_FLAG_FP32)) {
+        delete h;
+        return fail(SG_ERR_ARG, "sg_create: unknown flag");
+    }
     h->device = device; h->cap = capacity; h->flags = flags;
     h->max_partials = sg_strict::reduce_blocks(capacity);
     ce = cudaMalloc(&h->sd, sizeof(double) * sgk::SD_COUNT * capacity);
@@ -132,6 +145,7 @@ int sg_destroy(sg_handle h)
     cudaFree(h->sd); cudaFree(h->si); cudaFree(h->stats); cudaFree(h->partials);
     cudaFree(h->table); cudaFree(h->table_x0);
     cudaFree(h->defer_d); cudaFree(h->defer_i); cudaFree(h->defer_list); cudaFree(h->defer_count);
+    cudaFree(h->perm); cudaFree(h->sort_keys); cudaFree(h->sort_hist);
     delete h;
     return SG_OK;
 }
@@ -182,6 +196,8 @@ int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const 
     h->meal_minute = meal_minute; h->meal_grams = meal_grams; h->max_meals = max_meals;
     h->noise = noise; h->n_noise = n_noise;
     h->steps_done = 0;
+    h->perm_valid = false;
+    h->per_episode_positions = false;
     sgk::EpisodeArgs a = base_args(h);
     a.x0 = x0; a.row0 = row0; a.t0 = h->t0;
     cudaError_t ce = use_fma(h) ? sg_fma::launch_reset(a, (cudaStream_t)stream)
@@ -192,48 +208,81 @@ int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const 
     return SG_OK;
 }
 
+// Counting sort of the episodes by their next meal event (sg_coherence.cu) -> h->perm.
+static int sort_episodes(sg_handle h, cudaStream_t stream)
+{
+    sgc::SortArgs sa{};
+    sa.n = h->n; sa.cap = h->cap; sa.sd = h->sd; sa.si = h->si;
+    sa.meal_minute = h->meal_minute; sa.meal_grams = h->meal_grams; sa.max_meals = h->max_meals;
+    sa.window = h->coherence_steps * h->hw.st;
+    sa.n_keys = h->sort_n_keys;
+    sa.keys = h->sort_keys; sa.hist = h->sort_hist; sa.perm = h->perm;
+    cudaError_t ce = sgc::launch_sort(sa, stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_set_coherence: sort launch", ce);
+    h->launches += 3;
+    h->perm_valid = true;
+    h->steps_since_sort = 0;
+    return SG_OK;
+}
+
 static int run_impl(sg_handle h, int32_t controller, const double *ctrl_host, const double *ctrl_rows,
                     const double *basal, const double *bolus, int64_t act_stride, int32_t n_steps,
                     double *trace, int32_t *counters, void *stream, const char *who,
                     const double *step_meals = nullptr)
 {
     if (!h->is_reset) return fail(SG_ERR_STATE, who);
-    if (h->steps_done + n_steps + 2 > h->n_noise) return fail(SG_ERR_ARG, "noise stream too short for the requested steps");
+    // every episode started at the last sg_reset: the stream length is checked here; after sg_reset_masked the
+    // episodes have positions of their own and the kernel's guard reports an exhausted stream per episode (-5)
+    if (!h->per_episode_positions && h->steps_done + n_steps + 2 > h->n_noise)
+        return fail(SG_ERR_ARG, "noise stream too short for the requested steps");
     if (n_steps == 0) return SG_OK;
     DeviceGuard g(h->device);
     sgk::EpisodeArgs a = base_args(h);
     a.controller = controller;
+    a.step0 = h->steps_total;
     if (ctrl_host) memcpy(a.ctrl, ctrl_host, sizeof a.ctrl);
     a.ctrl_rows = ctrl_rows;
     a.act_basal = basal; a.act_bolus = bolus; a.act_stride = act_stride;
     a.n_steps = n_steps;
     a.trace = trace; a.counters = counters; a.step_meals = step_meals;
-    if (h->step_cap > 0) {
-        // one env-step per launch pair: phase A puts heavy minutes aside, phase B finishes them in full warps
-        for (int32_t k = 0; k < n_steps; k++) {
-            sgk::EpisodeArgs b = a;
-            b.n_steps = 1;
-            if (basal) { b.act_basal = basal + (int64_t)k * act_stride; b.act_bolus = bolus + (int64_t)k * act_stride; }
-            if (trace) b.trace = trace + (int64_t)k * sgk::NTRACE * h->n;
-            if (counters) b.counters = counters + (int64_t)k * h->hw.st * 2 * h->n;
-            cudaError_t ce = use_fma(h) ? sg_fma::launch_run_capped(b, (cudaStream_t)stream)
-                                        : sg_strict::launch_run_capped(b, (cudaStream_t)stream);
-            if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
-            h->launches += 2;
+    // The run is cut into launches: one env-step each with a step cap (phase A / phase B pairs), the env-steps up to the
+    // next sort with a coherent launch order, otherwise a single launch.
+    int32_t k = 0;
+    while (k < n_steps) {
+        int32_t len = n_steps - k;
+        if (h->step_cap > 0) len = 1;
+        if (h->coherence_steps > 0) {
+            if (!h->perm_valid || h->steps_since_sort >= h->coherence_steps) {
+                int rc = sort_episodes(h, (cudaStream_t)stream);
+                if (rc != SG_OK) return rc;
+            }
+            const int32_t left = h->coherence_steps - h->steps_since_sort;
+            if (left < len) len = left;
         }
-        h->steps_done += n_steps;
-        return SG_OK;
+        sgk::EpisodeArgs b = a;
+        b.perm = (h->coherence_steps > 0 && h->perm_valid) ? h->perm : nullptr;
+        b.n_steps = len;
+        b.step0 = h->steps_total;
+        if (basal) { b.act_basal = basal + (int64_t)k * act_stride; b.act_bolus = bolus + (int64_t)k * act_stride; }
+        if (trace) b.trace = trace + (int64_t)k * sgk::NTRACE * h->n;
+        if (counters) b.counters = counters + (int64_t)k * h->hw.st * 2 * h->n;
+        cudaError_t ce;
+        if (h->step_cap > 0) {
+            ce = use_fma(h) ? sg_fma::launch_run_capped(b, (cudaStream_t)stream)
+                            : sg_strict::launch_run_capped(b, (cudaStream_t)stream);
+            h->launches++;                                   // phase B
+        } else if (h->flags & SG_FLAG_FP32) {
+            ce = sg_fma::launch_run_fp32(b, (cudaStream_t)stream);
+        } else {
+            ce = use_fma(h) ? sg_fma::launch_run(b, (cudaStream_t)stream) : sg_strict::launch_run(b, (cudaStream_t)stream);
+        }
+        if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
+        h->launches++;
+        h->steps_done += len;
+        h->steps_total += len;
+        h->steps_since_sort += len;
+        k += len;
     }
-    cudaError_t ce;
-    if (h->flags & SG_FLAG_FP32)
-        ce = sg_fma::launch_run_fp32(a, (cudaStream_t)stream);
-    else if (h->flags & SG_FLAG_PAIR)
-        ce = use_fma(h) ? sg_fma::launch_run_pair(a, (cudaStream_t)stream) : sg_strict::launch_run_pair(a, (cudaStream_t)stream);
-    else
-        ce = use_fma(h) ? sg_fma::launch_run(a, (cudaStream_t)stream) : sg_strict::launch_run(a, (cudaStream_t)stream);
-    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, who, ce);
-    h->launches++;
-    h->steps_done += n_steps;
     return SG_OK;
 }
 
@@ -242,7 +291,7 @@ int sg_run(sg_handle h, int32_t controller, const double *ctrl_host, const doubl
 {
     if (!h) return fail(SG_ERR_ARG, "sg_run: null handle");
     if (n_steps < 0) return fail(SG_ERR_ARG, "sg_run: n_steps < 0");
-    if (controller < SG_CTRL_ACTIONS || controller > SG_CTRL_PID) return fail(SG_ERR_ARG, "sg_run: unknown controller");
+    if (controller < SG_CTRL_ACTIONS || controller > SG_CTRL_RANDOM) return fail(SG_ERR_ARG, "sg_run: unknown controller");
     if (controller == SG_CTRL_ACTIONS && !actions) return fail(SG_ERR_ARG, "sg_run: actions required");
     if (controller != SG_CTRL_ACTIONS && !ctrl_host && !ctrl_rows) return fail(SG_ERR_ARG, "sg_run: controller constants required");
     return run_impl(h, controller, ctrl_host, ctrl_rows, actions, actions ? actions + h->n : nullptr, 2 * h->n,
@@ -281,6 +330,8 @@ int sg_set_step_cap(sg_handle h, int32_t cap)
 {
     if (!h || cap < 0) return fail(SG_ERR_ARG, "sg_set_step_cap: bad arguments");
     if (cap > 0 && cap < 4) return fail(SG_ERR_ARG, "sg_set_step_cap: a cap below 4 steps would put ordinary minutes aside");
+    if (cap > 0 && (h->flags & SG_FLAG_FP32))
+        return fail(SG_ERR_ARG, "sg_set_step_cap: the heavy-minute kernels are FP64 only; not available with SG_FLAG_FP32");
     DeviceGuard g(h->device);
     if (cap > 0 && !h->defer_d) {
         cudaError_t ce = cudaMalloc(&h->defer_d, sizeof(double) * sgk::DEFER_ND * h->cap);
@@ -290,6 +341,60 @@ int sg_set_step_cap(sg_handle h, int32_t cap)
         if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_step_cap: cudaMalloc", ce);
     }
     h->step_cap = cap;
+    return SG_OK;
+}
+
+int sg_set_coherence(sg_handle h, int32_t segment_steps)
+{
+    if (!h || segment_steps < 0) return fail(SG_ERR_ARG, "sg_set_coherence: bad arguments");
+    if (segment_steps > 0 && !h->have_hw) return fail(SG_ERR_STATE, "sg_set_coherence: call sg_set_hardware first");
+    DeviceGuard g(h->device);
+    if (segment_steps > 0) {
+        const int64_t window = (int64_t)segment_steps * h->hw.st;
+        if (window > 4096) return fail(SG_ERR_ARG, "sg_set_coherence: at most 4096 minutes between two sorts");
+        const int32_t n_keys = sgc::key_count((int32_t)window);
+        if (!h->perm) {
+            cudaError_t ce = cudaMalloc(&h->perm, sizeof(int32_t) * h->cap);
+            if (ce == cudaSuccess) ce = cudaMalloc(&h->sort_keys, sizeof(int32_t) * h->cap);
+            if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_coherence: cudaMalloc", ce);
+        }
+        if (n_keys > h->sort_n_keys) {
+            cudaFree(h->sort_hist);
+            h->sort_hist = nullptr; h->sort_n_keys = 0;
+            cudaError_t ce = cudaMalloc(&h->sort_hist, sizeof(int32_t) * n_keys);
+            if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_coherence: cudaMalloc", ce);
+        }
+        h->sort_n_keys = n_keys;
+    }
+    h->coherence_steps = segment_steps;
+    h->perm_valid = false;
+    return SG_OK;
+}
+
+int sg_get_launch_order(sg_handle h, int32_t *perm_out, void *stream)
+{
+    if (!h || !perm_out) return fail(SG_ERR_ARG, "sg_get_launch_order: null argument");
+    if (!h->is_reset || h->coherence_steps == 0 || !h->perm_valid)
+        return fail(SG_ERR_STATE, "sg_get_launch_order: no sorted launch order (sg_set_coherence, then a step)");
+    DeviceGuard g(h->device);
+    cudaError_t ce = cudaMemcpyAsync(perm_out, h->perm, sizeof(int32_t) * h->n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_get_launch_order: copy", ce);
+    return SG_OK;
+}
+
+int sg_reset_masked(sg_handle h, const int32_t *mask, const double *x0, double *row0, void *stream)
+{
+    if (!h || !mask) return fail(SG_ERR_ARG, "sg_reset_masked: null argument");
+    if (!h->is_reset) return fail(SG_ERR_STATE, "sg_reset_masked: call sg_reset first");
+    if (!x0 && (!h->patient_row || !h->table_x0)) return fail(SG_ERR_ARG, "sg_reset_masked: need x0, or patient_row + sg_load_params");
+    DeviceGuard g(h->device);
+    sgk::EpisodeArgs a = base_args(h);
+    a.x0 = x0; a.row0 = row0; a.t0 = h->t0; a.reset_mask = mask;
+    cudaError_t ce = use_fma(h) ? sg_fma::launch_reset(a, (cudaStream_t)stream)
+                                : sg_strict::launch_reset(a, (cudaStream_t)stream);
+    if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_reset_masked: launch", ce);
+    h->launches++;
+    h->per_episode_positions = true;
     return SG_OK;
 }
 

@@ -223,9 +223,10 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
 {
     using namespace fp32;
     extern __shared__ float fsmem[];   // F_COUNT rows x FBLOCK columns
-    const int64_t e = (int64_t)blockIdx.x * FBLOCK + threadIdx.x;
-    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);
-    if (e >= a.n) return;
+    const int64_t idx = (int64_t)blockIdx.x * FBLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, idx < a.n);
+    if (idx >= a.n) return;
+    const int64_t e = a.perm ? (int64_t)a.perm[idx] : idx;         // schedule-coherent order (sg_set_coherence)
     const FCol c{fsmem + threadIdx.x};
     const ParamLoad p = param_source(a, e);
     stage_params_f(c, p);
@@ -267,7 +268,7 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
         const double obs = sd[(int64_t)SD_OBS * a.cap];
         if (a.controller == 1) {                       // BBController._bb_policy
             const double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
-            a_basal = p(P_u2ss) * BW / 6000.0;
+            a_basal = (ctrl[3] > 0.0) ? ctrl[3] : p(P_u2ss) * BW / 6000.0;   // see run_kernel
             if (info_meal > 0.0) {
                 const double corr = (obs > 150.0 ? 1.0 : 0.0) * (obs - ctrl[0]) / ctrl[2];
                 a_bolus = (info_meal * st) / ctrl[1] + corr;
@@ -279,6 +280,9 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
             a_basal = ctrl[0] * (obs - ctrl[3]) + ctrl[1] * pid_integ + ctrl[2] * (obs - pid_prev) / st;
             sd[(int64_t)SD_PID_PREV * a.cap] = obs;
             sd[(int64_t)SD_PID_INTEG * a.cap] = pid_integ + (obs - ctrl[3]) * st;
+        } else if (a.controller == 3) {                // random basal ~ U(ctrl[0], ctrl[1]), see run_kernel
+            sgp::Philox rng((uint64_t)ctrl[2], (uint64_t)ctrl[3] + (uint64_t)e, 0x6163746eu, (uint32_t)(a.step0 + k));
+            a_basal = ctrl[0] + (ctrl[1] - ctrl[0]) * rng.uniform();
         } else {
             a_basal = a.act_basal[(int64_t)k * a.act_stride + e];
             a_bolus = a.act_bolus[(int64_t)k * a.act_stride + e];
@@ -324,7 +328,7 @@ __global__ void __launch_bounds__(fp32::FBLOCK, 3) run_fp32_kernel(const Episode
             step_nrej += cnt.nrej;
             minute++;
             const double bg = sgm::div_r((double)x[12], Vg, r_Vg);            // t1dpatient.py:217-218
-            if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
+            if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos, status);   // cgm.py:27
             CHO += sgm::div_r(announced, st, r_st); insulin += ins_mean;
             BG += sgm::div_r(bg, st, r_st); CGM += sgm::div_r(last_cgm, st, r_st);
         }

@@ -14,74 +14,41 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "sg_philox.cuh"
+
 namespace {
 
-struct Philox {
-    uint32_t key[2];
-    uint32_t ctr[4];
-    uint32_t out[4];
-    int have;
-
-    __device__ Philox(uint64_t seed, uint64_t stream, uint32_t substream)
-    {
-        key[0] = (uint32_t)seed; key[1] = (uint32_t)(seed >> 32);
-        ctr[0] = 0; ctr[1] = substream; ctr[2] = (uint32_t)stream; ctr[3] = (uint32_t)(stream >> 32);
-        have = 0;
-    }
-    __device__ void round(uint32_t (&c)[4], const uint32_t (&k)[2])
-    {
-        const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
-        const uint32_t hi0 = __umulhi(M0, c[0]), lo0 = M0 * c[0];
-        const uint32_t hi1 = __umulhi(M1, c[2]), lo1 = M1 * c[2];
-        const uint32_t n0 = hi1 ^ c[1] ^ k[0], n1 = lo1, n2 = hi0 ^ c[3] ^ k[1], n3 = lo0;
-        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
-    }
-    __device__ void refill()
-    {
-        uint32_t c[4] = {ctr[0], ctr[1], ctr[2], ctr[3]};
-        uint32_t k[2] = {key[0], key[1]};
-#pragma unroll
-        for (int r = 0; r < 10; r++) {
-            round(c, k);
-            k[0] += 0x9E3779B9u; k[1] += 0xBB67AE85u;
-        }
-        out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
-        ctr[0]++;
-        have = 4;
-    }
-    __device__ uint32_t next32()
-    {
-        if (have == 0) refill();
-        return out[--have];
-    }
-    // uniform in (0, 1), 53 bits
-    __device__ double uniform()
-    {
-        const uint64_t a = next32(), b = next32();
-        const uint64_t bits = ((a << 32) | b) >> 11;
-        return ((double)bits + 0.5) * (1.0 / 9007199254740992.0);
-    }
-    __device__ double normal()
-    {
-        // inverse-CDF normal: one uniform per draw, monotone, no rejection
-        return normcdfinv(uniform());
-    }
-};
+using sgp::Philox;
 
 constexpr int MAX_W = 151 * 11;   // Navigator: 151 samples per window
 
 // CGMNoise: AR(1)-type chain at 15-minute knots, Johnson SU transform, cubic interpolation to the
 // sensor grid expressed as a constant matrix W [(nsample) x 11] (row 0 = the carried knot, dropped).
+// Which stream an episode draws from, and whether it is written at all.  Positional: episodes (ep0 + e) / group share a
+// stream (the 30 patients of one seed group).  Keyed: key[e] names the stream (a vector environment restarts its
+// episodes one by one: key = env index + num_envs * episodes started so far) and only columns with mask[e] != 0 are
+// rewritten (mask null = all).
+struct StreamSel {
+    int64_t ep0, group;
+    const int64_t *key;
+    const int32_t *mask;
+    __device__ __forceinline__ bool skip(int64_t e) const { return mask && mask[e] == 0; }
+    __device__ __forceinline__ uint64_t stream(int64_t e) const
+    {
+        return key ? (uint64_t)key[e] : (uint64_t)((ep0 + e) / group);
+    }
+};
+
 __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
                                                    const double *W, double pacf, double gamma, double lambda,
-                                                   double delta, double xi, uint64_t seed, int64_t ep0, int64_t group)
+                                                   double delta, double xi, uint64_t seed, const StreamSel sel)
 {
     extern __shared__ double sW[];
     for (int i = threadIdx.x; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
     __syncthreads();
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= n) return;
-    Philox rng(seed, (uint64_t)((ep0 + e) / group), 0x6e6f6973u /* 'nois' */);
+    if (e >= n || sel.skip(e)) return;
+    Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
     double ar = rng.normal();                                   // noise_gen.py:84-85
     double knots[11];
     knots[10] = xi + lambda * sinh((ar - gamma) / delta);       // _noise_init, noise_gen.py:24
@@ -104,16 +71,17 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
 
 // RandomScenario: one schedule per calendar day, six candidate meals (scenario_gen.py:38-58).
 __global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, double *meal_grams, int64_t n,
-                                                      int max_meals, int start_minute, int horizon,
-                                                      uint64_t seed, int64_t ep0, int64_t group)
+                                                      int max_meals, int start_minute_all, const int32_t *start_minute_rows,
+                                                      int horizon, uint64_t seed, const StreamSel sel)
 {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= n) return;
+    if (e >= n || sel.skip(e)) return;
+    const int start_minute = start_minute_rows ? start_minute_rows[e] : start_minute_all;
     const double prob[6] = {0.95, 0.3, 0.95, 0.3, 0.95, 0.3};
     const double lb[6] = {300, 540, 600, 840, 960, 1200}, ub[6] = {540, 600, 840, 960, 1200, 1380};
     const double mu[6] = {420, 570, 720, 900, 1080, 1290}, sd[6] = {60, 30, 60, 30, 60, 30};
     const double amu[6] = {45, 10, 70, 10, 80, 10}, asd[6] = {10, 5, 10, 5, 10, 5};
-    Philox rng(seed, (uint64_t)((ep0 + e) / group), 0x6d65616cu /* 'meal' */);
+    Philox rng(seed, sel.stream(e), 0x6d65616cu /* 'meal' */);
     int pos = 0, last = -1;
     const int n_days = (start_minute + horizon + 1439) / 1440;
     for (int day = 0; day < n_days; day++) {
@@ -142,6 +110,37 @@ __global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, dou
 }
 
 // params_soa[i][e] = table[row[e]][i] * (1 + amp * u), u ~ U(-1, 1) i.i.d. per parameter.
+// Where and how an episode starts, as the gym wrapper draws it (envs/simglucose_gym_env.py:58-73): start hour
+// ~ randint(0, 24), and T1DPatient(random_init_bg=True): x[3], x[4], x[12] ~ N(mean, 0.1 * mean) independently
+// (multivariate_normal with a diagonal covariance, t1dpatient.py:256-270).  n_draws successive randomisations, each
+// around the result of the one before with the SAME three deviates: the wrapper resets the patient twice (constructor
+// and env.reset()) with RandomState(seed) re-created each time and init_state mutated in place.
+__global__ void __launch_bounds__(128) episode_start_kernel(int32_t *start_minute, double *x0, const double *table_x0,
+                                                           const int32_t *row, int64_t n, int n_draws, uint64_t seed,
+                                                           const StreamSel sel)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n || sel.skip(e)) return;
+    Philox rng(seed, sel.stream(e), 0x73746172u /* 'star' */);
+    const double uh = rng.uniform();
+    const double z3 = rng.normal(), z4 = rng.normal(), z12 = rng.normal();
+    if (start_minute) {
+        int hour = (int)(uh * 24.0);
+        start_minute[e] = 60 * (hour > 23 ? 23 : hour);
+    }
+    if (x0) {
+        const double *t = table_x0 + (int64_t)row[e] * SG_NX;
+        double v3 = t[3], v4 = t[4], v12 = t[12];
+        for (int d = 0; d < n_draws; d++) {
+            v3 = v3 + sqrt(0.1 * v3) * z3;
+            v4 = v4 + sqrt(0.1 * v4) * z4;
+            v12 = v12 + sqrt(0.1 * v12) * z12;
+        }
+#pragma unroll
+        for (int i = 0; i < SG_NX; i++) x0[(int64_t)i * n + e] = (i == 3) ? v3 : (i == 4) ? v4 : (i == 12) ? v12 : t[i];
+    }
+}
+
 __global__ void __launch_bounds__(128) perturb_kernel(double *params_soa, const double *table, const int32_t *row,
                                                      int64_t n, double amp, uint64_t seed, int64_t ep0, int64_t group)
 {
@@ -179,7 +178,18 @@ int sg_gen_noise(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsamp
         return SG_ERR_ARG;
     noise_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
         out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
-        model_host[4], seed, episode_offset, group_size);
+        model_host[4], seed, StreamSel{episode_offset, group_size, nullptr, nullptr});
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_noise_keyed(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsample, const double *W_dev,
+                       const double *model_host, uint64_t seed, const int64_t *key, const int32_t *mask, void *stream)
+{
+    if (!out || !W_dev || !model_host || !key || n_episodes <= 0 || n_noise <= 0 || nsample < 2 || nsample * 11 > MAX_W)
+        return SG_ERR_ARG;
+    noise_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+        out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
+        model_host[4], seed, StreamSel{0, 1, key, mask});
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 
@@ -191,7 +201,30 @@ int sg_gen_scenarios(int32_t *meal_minute, double *meal_grams, int64_t n_episode
         start_minute >= 1440 || horizon_minutes <= 0 || group_size < 1)
         return SG_ERR_ARG;
     scenario_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
-        meal_minute, meal_grams, n_episodes, max_meals, start_minute, horizon_minutes, seed, episode_offset, group_size);
+        meal_minute, meal_grams, n_episodes, max_meals, start_minute, nullptr, horizon_minutes, seed,
+        StreamSel{episode_offset, group_size, nullptr, nullptr});
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_scenarios_keyed(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
+                           const int32_t *start_minute, int32_t horizon_minutes, uint64_t seed, const int64_t *key,
+                           const int32_t *mask, void *stream)
+{
+    if (!meal_minute || !meal_grams || !start_minute || !key || n_episodes <= 0 || max_meals <= 0 || horizon_minutes <= 0)
+        return SG_ERR_ARG;
+    scenario_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
+        meal_minute, meal_grams, n_episodes, max_meals, 0, start_minute, horizon_minutes, seed, StreamSel{0, 1, key, mask});
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_episode_starts(int32_t *start_minute, double *x0, const double *table_x0_dev, const int32_t *patient_row,
+                          int64_t n_episodes, int32_t n_draws, uint64_t seed, const int64_t *key, const int32_t *mask,
+                          void *stream)
+{
+    if ((!start_minute && !x0) || !key || n_episodes <= 0 || n_draws < 0 || (x0 && (!table_x0_dev || !patient_row)))
+        return SG_ERR_ARG;
+    episode_start_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
+        start_minute, x0, table_x0_dev, patient_row, n_episodes, n_draws, seed, StreamSel{0, 1, key, mask});
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 

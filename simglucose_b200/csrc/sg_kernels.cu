@@ -9,6 +9,7 @@
 // reduce_*      population statistics (warp shuffles -> block partials -> fixed-order pass)
 #include "sg_kernels.cuh"
 #include "sg_model.cuh"
+#include "sg_philox.cuh"
 
 #ifndef SG_NS
 #error "compile with -DSG_NS=sg_strict or -DSG_NS=sg_fma"
@@ -30,11 +31,15 @@ __device__ __forceinline__ ParamLoad param_source(const EpisodeArgs &a, int64_t 
 }
 
 // CGMSensor.measure at a sampling minute, cgm.py:28-33.
-__device__ __forceinline__ double cgm_sample(const EpisodeArgs &a, int64_t e, double bg, int &noise_pos)
+__device__ __forceinline__ double cgm_sample(const EpisodeArgs &a, int64_t e, double bg, int &noise_pos, int &status)
 {
-    // the C-ABI checks the stream length against the steps taken; the guard covers episode states that were
-    // uploaded with a position of their own (sg_set_episode_state)
-    double cgm = bg + (noise_pos < a.n_noise ? a.noise[(int64_t)noise_pos * a.n + e] : 0.0);
+    // the C-ABI checks the stream length against the steps taken when every episode started together; episodes with
+    // a position of their own (sg_reset_masked, sg_set_episode_state) are guarded here: a sample beyond the bound
+    // stream reads as zero noise and marks the episode (sg_get_status: -5), it never reads out of bounds
+    double nz = 0.0;
+    if (noise_pos < a.n_noise) nz = a.noise[(int64_t)noise_pos * a.n + e];
+    else if (status > 0) status = STATUS_STREAM_EXHAUSTED;
+    double cgm = bg + nz;
     noise_pos++;
     cgm = (a.hw.smin > cgm) ? a.hw.smin : cgm;   // max(CGM, min)
     cgm = (a.hw.smax < cgm) ? a.hw.smax : cgm;   // min(CGM, max)
@@ -77,6 +82,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
 {
     const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     if (e >= a.n) return;
+    if (a.reset_mask && a.reset_mask[e] == 0) return;       // sg_reset_masked: this episode keeps running
     const ParamLoad p = param_source(a, e);
     const double Vg = p(P_Vg);
     double x[NX];
@@ -102,9 +108,14 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
     const double bg = x[12] / Vg;
     double lbgi, hbgi, ri;
     risk_index(bg, lbgi, hbgi, ri);
-    int noise_pos = 0;
-    const double cgm0 = cgm_sample(a, e, bg, noise_pos);    // CGM_hist[0]
-    const double obs = cgm_sample(a, e, bg, noise_pos);     // returned observation
+    // sensor.measure samples only when patient.t % sample_time == 0 (cgm.py:27); otherwise it returns the value held
+    // since sensor.reset(), 0 (cgm.py:47-50), and no noise is consumed
+    int noise_pos = 0, status = 1;
+    double cgm0 = 0.0, obs = 0.0;
+    if (a.t0 % a.hw.st == 0) {
+        cgm0 = cgm_sample(a, e, bg, noise_pos, status);     // CGM_hist[0]
+        obs = cgm_sample(a, e, bg, noise_pos, status);      // returned observation
+    }
     sd[(int64_t)SD_LAST_CGM * a.cap] = obs;
     sd[(int64_t)SD_CGM_PREV * a.cap] = cgm0;
     sd[(int64_t)SD_OBS * a.cap] = obs;
@@ -115,7 +126,7 @@ __global__ void __launch_bounds__(BLOCK) reset_kernel(const EpisodeArgs a)
     si[(int64_t)SI_MINUTE * a.cap] = a.t0;
     si[(int64_t)SI_NOISE_POS * a.cap] = noise_pos;
     si[(int64_t)SI_MEAL_POS * a.cap] = 0;
-    si[(int64_t)SI_STATUS * a.cap] = 1;
+    si[(int64_t)SI_STATUS * a.cap] = status;
     double s[NSTAT];
 #pragma unroll
     for (int i = 0; i < NSTAT; i++) s[i] = 0.0;
@@ -206,7 +217,10 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
         const double obs = sd[(int64_t)SD_OBS * a.cap];
         if (a.controller == 1) {                       // BBController._bb_policy
             const double info_meal = sd[(int64_t)SD_INFO_MEAL * a.cap];
-            a_basal = sgm::div_ieee(__ldg(&p.base[P_u2ss * p.stride]) * c(H_BW), 6000.0);
+            // basal = u2ss * BW / 6000 of the CSV row the controller finds by patient NAME (basal_bolus_ctrller.py:52-64):
+            // ctrl[3] when the caller supplies it (perturbed populations keep the nominal basal), else the episode's
+            // own parameter row
+            a_basal = (ctrl[3] > 0.0) ? ctrl[3] : c(H_BASAL);
             if (info_meal > 0.0) {
                 const double corr = sgm::div_ieee((obs > 150.0 ? 1.0 : 0.0) * (obs - ctrl[0]), ctrl[2]);
                 a_bolus = sgm::div_ieee(info_meal * st, ctrl[1]) + corr;
@@ -220,6 +234,13 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
             a_basal = ctrl[0] * (obs - ctrl[3]) + ctrl[1] * pid_integ + sgm::div_ieee(ctrl[2] * (obs - pid_prev), st);
             sd[(int64_t)SD_PID_PREV * a.cap] = obs;
             sd[(int64_t)SD_PID_INTEG * a.cap] = pid_integ + (obs - ctrl[3]) * st;
+            a_bolus = 0.0;
+        } else if (a.controller == 3) {                // random basal rate ~ U(ctrl[0], ctrl[1]), bolus 0: the action
+            // gym's action_space.sample() would hand the wrapper (simglucose_gym_env.py:41-46), drawn in the kernel from
+            // Philox keyed by (seed = ctrl[2], global episode index = ctrl[3] + e, env-step index)
+            sgp::Philox rng((uint64_t)ctrl[2], (uint64_t)ctrl[3] + (uint64_t)e, 0x6163746eu /* 'actn' */,
+                            (uint32_t)(a.step0 + k));
+            a_basal = ctrl[0] + (ctrl[1] - ctrl[0]) * rng.uniform();
             a_bolus = 0.0;
         } else {
             a_basal = a.act_basal[(int64_t)k * a.act_stride + e];
@@ -291,7 +312,7 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
             step_nrej += cnt.nrej;
             minute++;
             const double bg = sgm::div_r(x[12], c(H_Vg), c(H_rVg));      // t1dpatient.py:217-218
-            if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos);   // cgm.py:27
+            if (minute % st_i == 0) last_cgm = cgm_sample(a, e, bg, noise_pos, status);   // cgm.py:27
             CHO += sgm::div_r(announced, st, r_st); insulin += ins_mean;
             BG += sgm::div_r(bg, st, r_st); CGM += sgm::div_r(last_cgm, st, r_st);
         }
@@ -339,18 +360,20 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
 __global__ void __launch_bounds__(BLOCK) run_kernel(const EpisodeArgs a)
 {
     extern __shared__ double smem[];   // H_COUNT rows x BLOCK columns
-    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
-    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);   // the lanes that own an episode
-    if (e >= a.n) return;          // no block-level synchronisation below: columns are private
+    const int64_t idx = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, idx < a.n);   // the lanes that own an episode
+    if (idx >= a.n) return;        // no block-level synchronisation below: columns are private
+    const int e = a.perm ? a.perm[idx] : (int)idx;                 // schedule-coherent order (sg_set_coherence)
     episode_steps<RUN_PLAIN>(a, e, lanes, smem);
 }
 
 __global__ void __launch_bounds__(BLOCK) run_capped_kernel(const EpisodeArgs a)
 {
     extern __shared__ double smem[];
-    const int64_t e = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
-    const unsigned lanes = __ballot_sync(0xffffffffu, e < a.n);
-    if (e >= a.n) return;
+    const int64_t idx = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
+    const unsigned lanes = __ballot_sync(0xffffffffu, idx < a.n);
+    if (idx >= a.n) return;
+    const int e = a.perm ? a.perm[idx] : (int)idx;
     episode_steps<RUN_CAPPED>(a, e, lanes, smem);
 }
 
@@ -576,6 +599,22 @@ __global__ void reduce_final_kernel(const ReduceArgs a)
 // ---- launchers --------------------------------------------------------------------------------
 static inline unsigned grid_for(int64_t n) { return (unsigned)((n + BLOCK - 1) / BLOCK); }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to the (kernel, device) pair: a process that creates handles on
+// several GPUs has to raise it on each of them.  `done` is the launcher's own per-device record.
+constexpr int MAX_DEVICES = 64;
+template <class Kernel>
+static cudaError_t allow_dynamic_smem(Kernel kernel, int bytes, bool (&done)[MAX_DEVICES])
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const bool tracked = dev >= 0 && dev < MAX_DEVICES;
+    if (tracked && done[dev]) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && tracked) done[dev] = true;
+    return e;
+}
+
 cudaError_t launch_reset(const EpisodeArgs &a, cudaStream_t s)
 {
     reset_kernel<<<grid_for(a.n), BLOCK, 0, s>>>(a);
@@ -585,12 +624,9 @@ cudaError_t launch_reset(const EpisodeArgs &a, cudaStream_t s)
 cudaError_t launch_run(const EpisodeArgs &a, cudaStream_t s)
 {
     constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    static bool done[MAX_DEVICES] = {};
+    cudaError_t e = allow_dynamic_smem(run_kernel, kSmem, done);
+    if (e != cudaSuccess) return e;
     run_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
     return cudaGetLastError();
 }
@@ -599,14 +635,11 @@ cudaError_t launch_run(const EpisodeArgs &a, cudaStream_t s)
 cudaError_t launch_run_capped(const EpisodeArgs &a, cudaStream_t s)
 {
     constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(run_capped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(run_resume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
-    cudaError_t e = cudaMemsetAsync(a.defer_count, 0, sizeof(int32_t), s);
+    static bool done_a[MAX_DEVICES] = {}, done_b[MAX_DEVICES] = {};
+    cudaError_t e = allow_dynamic_smem(run_capped_kernel, kSmem, done_a);
+    if (e == cudaSuccess) e = allow_dynamic_smem(run_resume_kernel, kSmem, done_b);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(a.defer_count, 0, sizeof(int32_t), s);
     if (e != cudaSuccess) return e;
     run_capped_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
     e = cudaGetLastError();
@@ -617,7 +650,6 @@ cudaError_t launch_run_capped(const EpisodeArgs &a, cudaStream_t s)
     return cudaGetLastError();
 }
 
-#include "sg_pair.cuh"
 #ifdef SG_WITH_FP32
 #include "sg_fp32.cuh"
 #endif
@@ -625,12 +657,9 @@ cudaError_t launch_run_capped(const EpisodeArgs &a, cudaStream_t s)
 cudaError_t launch_patient_step(const PatientArgs &a, cudaStream_t s)
 {
     constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(patient_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    static bool done[MAX_DEVICES] = {};
+    cudaError_t e = allow_dynamic_smem(patient_step_kernel, kSmem, done);
+    if (e != cudaSuccess) return e;
     patient_step_kernel<<<grid_for(a.e.n), BLOCK, kSmem, s>>>(a);
     return cudaGetLastError();
 }
@@ -638,12 +667,9 @@ cudaError_t launch_patient_step(const PatientArgs &a, cudaStream_t s)
 cudaError_t launch_model(const ModelArgs &a, cudaStream_t s)
 {
     constexpr int kSmem = H_COUNT * BLOCK * (int)sizeof(double);
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(model_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    static bool done[MAX_DEVICES] = {};
+    cudaError_t e = allow_dynamic_smem(model_kernel, kSmem, done);
+    if (e != cudaSuccess) return e;
     model_kernel<<<grid_for(a.n), BLOCK, kSmem, s>>>(a);
     return cudaGetLastError();
 }

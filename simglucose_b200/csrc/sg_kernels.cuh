@@ -27,7 +27,7 @@ enum StateI {
     SI_MINUTE,                 // patient.t as an integer minute   t1dpatient.py:73-75
     SI_NOISE_POS,              // samples consumed from the noise stream
     SI_MEAL_POS,               // next unconsumed entry of the meal table
-    SI_STATUS,                 // scipy idid of the first failed minute, else 1
+    SI_STATUS,                 // scipy idid of the first failed minute (-5: noise stream exhausted), else 1
     SI_COUNT
 };
 
@@ -46,9 +46,14 @@ struct Hardware {
     double pump[6];
 };
 
+constexpr int STATUS_STREAM_EXHAUSTED = -5;   // the episode asked for a noise sample beyond the bound stream
+
 struct EpisodeArgs {
     int64_t n;                 // episodes
     int64_t cap;               // stride of the resident state arrays
+    // Schedule-coherent launch order (sg_set_coherence): thread i owns episode perm[i]; null = identity.  Only the
+    // thread -> episode mapping moves: every array stays indexed by the episode, so results do not depend on it.
+    const int32_t *perm;
     double *sd;
     int32_t *si;
     double *stats;             // [NSTAT][cap]
@@ -67,6 +72,7 @@ struct EpisodeArgs {
     int32_t carry_h;
     // run
     int32_t controller;
+    int64_t step0;             // env-steps this handle has launched so far (SG_CTRL_RANDOM: Philox counter)
     double ctrl[NCTRL];
     const double *ctrl_rows;   // [NCTRL][n] or null
     const double *act_basal;   // step k of episode e at act_basal[k * act_stride + e]
@@ -86,6 +92,7 @@ struct EpisodeArgs {
     const double *x0;          // [13][n] or null
     double *row0;              // [NTRACE][n] or null
     int32_t t0;                // patient.t at reset (T1DPatient(t0=...), t1dpatient.py:27,277)
+    const int32_t *reset_mask; // [n] or null: only episodes with a non-zero entry are reset (sg_reset_masked)
 };
 
 // T1DPatient.step for every episode: one minute with an explicit Action(CHO announced, insulin).
@@ -129,7 +136,6 @@ struct ReduceArgs {
     cudaError_t launch_reset(const sgk::EpisodeArgs &a, cudaStream_t s);      \
     cudaError_t launch_run(const sgk::EpisodeArgs &a, cudaStream_t s);        \
     cudaError_t launch_run_capped(const sgk::EpisodeArgs &a, cudaStream_t s); \
-    cudaError_t launch_run_pair(const sgk::EpisodeArgs &a, cudaStream_t s);   \
     cudaError_t launch_reduce(const sgk::ReduceArgs &a, cudaStream_t s);      \
     cudaError_t launch_patient_step(const sgk::PatientArgs &a, cudaStream_t s); \
     cudaError_t launch_model(const sgk::ModelArgs &a, cudaStream_t s);        \
@@ -146,3 +152,24 @@ struct ReduceArgs {
 SG_DECLARE_LAUNCHERS(sg_strict)
 SG_DECLARE_LAUNCHERS(sg_fma)
 namespace sg_fma { cudaError_t launch_run_fp32(const sgk::EpisodeArgs &a, cudaStream_t s); }   // built with FMA contraction only
+
+// Schedule-coherent launch order (sg_coherence.cu): a counting sort of the episodes by the minute of their next
+// meal event, so that the lanes of a warp meet the expensive minutes (meal onset / offset, bolus) together.
+namespace sgc {
+constexpr int GRAM_BUCKETS = 128;
+struct SortArgs {
+    int64_t n, cap;
+    const double *sd;
+    const int32_t *si;
+    const int32_t *meal_minute;    // [max_meals][n]
+    const double *meal_grams;
+    int32_t max_meals;
+    int32_t window;                // minutes ahead that are told apart (the segment until the next sort)
+    int32_t n_keys;                // key_count(window)
+    int32_t *keys;                 // [cap] scratch
+    int32_t *hist;                 // [n_keys] scratch: counts, then running offsets
+    int32_t *perm;                 // [cap] out: thread i of the next launches owns episode perm[i]
+};
+inline int32_t key_count(int32_t window) { return (window + 1) * GRAM_BUCKETS + 1; }
+cudaError_t launch_sort(const SortArgs &a, cudaStream_t s);    // memset + 3 kernels
+}  // namespace sgc

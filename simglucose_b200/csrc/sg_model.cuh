@@ -42,7 +42,7 @@ enum Hoisted {
     // Dbar the H_aa..H_dD rows were computed for, the risk index of the previous env-step's CGM (risk_diff)
     H_rVg, H_Dbar, H_RPREV,
     H_L4,                      // log of 1e-4, the floor of DOPCOR's facold (step_control works on logarithms)
-    H_pad0,
+    H_BASAL,                   // u2ss * BW / 6000: BBController's basal from the episode's own row (basal_bolus_ctrller.py:64)
     // per-thread scratch vectors of the integrator, NV = 14 rows each (13 states + one pad row, so that states
     // (2k, 2k+1) form a pair): k1 of the current step (needed again only after a rejected step and by HINIT), the two
     // longest-lived stage accumulators (see dopri5_minute) and the accepted state y of the integrator
@@ -112,6 +112,7 @@ __device__ __forceinline__ void stage_params(const ColT &c, Load p)
     c.set(H_rBW, sgm::rcp_nr(p(P_BW))); c.set(H_rVi, sgm::rcp_nr(p(P_Vi)));
     c.set(H_rVg, sgm::rcp_nr(p(P_Vg))); c.set(H_Dbar, 0.0); c.set(H_RPREV, 0.0);
     c.set(H_L4, sgm::log_pos(1.0e-4));
+    c.set(H_BASAL, sgm::div_ieee(p(P_u2ss) * p(P_BW), 6000.0));
 }
 
 // Inputs of the ODE that are constant over one simulated minute (t1dpatient.py:110:

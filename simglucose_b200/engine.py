@@ -28,14 +28,16 @@ class BatchEngine:
     T1DSimEnv (simulation/env.py:36-180) driven by SimObj.simulate (simulation/sim_engine.py:29-39).
     """
 
-    def __init__(self, capacity, device=0, carry_h=False, fma=False, sensor='Dexcom', pump='Insulet', pair=False, fp32=False):
+    def __init__(self, capacity, device=0, carry_h=False, fma=False, sensor='Dexcom', pump='Insulet', fp32=False,
+                 coherence=0):
+        """coherence: env-steps between two sorts of the launch order (set_coherence); 0 = off."""
         if not torch.cuda.is_available():
             raise _capi.SgError('simglucose_b200 needs a CUDA device (there is no CPU fallback)')
         self.lib = _capi.load()
         self.device = torch.device('cuda', device)
         self.capacity = int(capacity)
         self.flags = ((_capi.FLAG_CARRY_H if carry_h else 0) | (_capi.FLAG_FMA if fma else 0) |
-                      (_capi.FLAG_PAIR if pair else 0) | (_capi.FLAG_FP32 if fp32 else 0))
+                      (_capi.FLAG_FP32 if fp32 else 0))
         h = C.c_void_p()
         _capi.check(self.lib.sg_create(self.device.index, self.capacity, self.flags, C.byref(h)))
         self._h = h
@@ -44,6 +46,10 @@ class BatchEngine:
         self.set_hardware(sensor, pump)
         tbl, x0 = P.cohort_table()
         self.load_table(tbl, x0)
+        self.step_cap = 0
+        self.coherence = 0
+        if coherence:
+            self.set_coherence(coherence)
 
     # -- configuration ---------------------------------------------------------------------------
     def set_hardware(self, sensor='Dexcom', pump='Insulet'):
@@ -150,6 +156,30 @@ class BatchEngine:
         _capi.check(self.lib.sg_set_step_cap(self._h, int(cap)))
         self.step_cap = int(cap)
 
+    def set_coherence(self, segment_steps):
+        """Schedule-coherent launch order (sg_set_coherence): every `segment_steps` env-steps the episodes are sorted
+        by the minute of their next meal event, so that the lanes of a warp meet the expensive minutes together.
+        For populations whose episodes have meal schedules of their own; per-episode results do not change.  0 = off."""
+        _capi.check(self.lib.sg_set_coherence(self._h, int(segment_steps)))
+        self.coherence = int(segment_steps)
+
+    def launch_order(self):
+        """The current sorted launch order [E] int32 (thread i owns episode perm[i])."""
+        out = torch.empty(self.n, dtype=torch.int32, device=self.device)
+        _capi.check(self.lib.sg_get_launch_order(self._h, _ptr(out), _stream_ptr()))
+        return out
+
+    def reset_masked(self, mask, x0=None, row0=None):
+        """T1DSimEnv.reset for the episodes with mask != 0 only (sg_reset_masked).  The caller has already rewritten
+        the masked columns of the noise / meal buffers handed to reset() (they are borrowed, not copied: in-place
+        writes to those tensors are what the kernels read).  x0 [13, E]: post-reset states (None: table x0).
+        row0 [NTRACE, E]: receives history row 0 of the masked episodes (other columns untouched)."""
+        m = self._dev(mask, torch.int32, 1)
+        x0t = self._dev(x0, torch.float64, _capi.NX)
+        self._keep.update(mask=m, x0m=x0t)
+        _capi.check(self.lib.sg_reset_masked(self._h, _ptr(m), _ptr(x0t), _ptr(row0), _stream_ptr()))
+        return row0
+
     def set_t0(self, t0):
         """patient.t at the next reset (T1DPatient(t0=...), t1dpatient.py:27,277)."""
         _capi.check(self.lib.sg_set_t0(self._h, int(t0)))
@@ -167,10 +197,13 @@ class BatchEngine:
     def run(self, n_steps, controller='bb', ctrl=None, ctrl_rows=None, actions=None, trace=True, counters=False):
         """SimObj.simulate for every episode, n_steps env-steps in one launch.
 
-        controller: 'bb' (ctrl = target, CR, CF), 'pid' (ctrl = P, I, D, target) or 'actions'
-        (actions [n_steps, 2, E]).  ctrl_rows [4, E] overrides ctrl per episode.
+        controller: 'bb' (ctrl = target, CR, CF, basal -- basal 0: from the episode's own parameter row), 'pid'
+        (ctrl = P, I, D, target), 'random' (ctrl = lo, hi, seed, global index of episode 0: basal ~ U(lo, hi) drawn in
+        the kernel) or 'actions' (actions [n_steps, 2, E]).  ctrl_rows [4, E] overrides ctrl per episode.
+        trace may be a preallocated [n_steps, NTRACE, E] tensor.
         Returns dict(trace [n_steps, NTRACE, E] | None, counters [n_steps*st, 2, E] | None)."""
-        kind = {'actions': _capi.CTRL_ACTIONS, 'bb': _capi.CTRL_BB, 'pid': _capi.CTRL_PID}[controller]
+        kind = {'actions': _capi.CTRL_ACTIONS, 'bb': _capi.CTRL_BB, 'pid': _capi.CTRL_PID,
+                'random': _capi.CTRL_RANDOM}[controller]
         cbuf = None
         if ctrl is not None:
             c = list(ctrl) + [0.0] * (_capi.NCTRL - len(ctrl))
@@ -181,7 +214,11 @@ class BatchEngine:
             act = actions if isinstance(actions, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(actions))
             act = act.to(device=self.device, dtype=torch.float64).contiguous()
             assert tuple(act.shape) == (n_steps, 2, self.n)
-        tr = torch.empty(n_steps, _capi.NTRACE, self.n, dtype=torch.float64, device=self.device) if trace else None
+        if isinstance(trace, torch.Tensor):
+            tr = trace
+            assert tr.is_contiguous() and tr.numel() == n_steps * _capi.NTRACE * self.n and tr.dtype == torch.float64
+        else:
+            tr = torch.empty(n_steps, _capi.NTRACE, self.n, dtype=torch.float64, device=self.device) if trace else None
         cn = (torch.empty(n_steps * self.sample_time, 2, self.n, dtype=torch.int32, device=self.device)
               if counters else None)
         _capi.check(self.lib.sg_run(self._h, kind, cbuf, _ptr(cr), _ptr(act), int(n_steps), _ptr(tr), _ptr(cn),

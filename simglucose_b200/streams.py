@@ -304,6 +304,77 @@ def device_scenarios(n_episodes, horizon_minutes, start_minute=0, seed=0, episod
     return mm, mg
 
 
+def _noise_model(s):
+    return (C.c_double * 5)(s['PACF'], s['gamma'], s['lambda'], s['delta'], s['xi'])
+
+
+def device_noise_keyed(out, key, sensor='Dexcom', seed=0, mask=None, W=None):
+    """Rewrite columns of the noise buffer out [n_noise, E] in place: episode e draws the Philox stream named by
+    key[e] (int64 device tensor); only columns with mask[e] != 0 (int32 device tensor, None = all) are written.
+    W: the device copy of interp_matrix(sample_time), for callers that generate every step (no upload, no sync)."""
+    import torch
+    from . import _capi
+    lib = _capi.load()
+    s = P.sensor_params(sensor) if isinstance(sensor, str) else sensor
+    dev = out.device
+    own_W = W is None
+    if own_W:
+        W = torch.from_numpy(interp_matrix(s['sample_time'])).to(dev)
+    assert out.is_contiguous() and key.dtype == torch.int64 and (mask is None or mask.dtype == torch.int32)
+    with torch.cuda.device(dev):
+        _capi.check(lib.sg_gen_noise_keyed(C.c_void_p(out.data_ptr()), out.shape[1], out.shape[0], W.shape[0],
+                                           C.c_void_p(W.data_ptr()), _noise_model(s), seed, C.c_void_p(key.data_ptr()),
+                                           C.c_void_p(mask.data_ptr()) if mask is not None else None, _stream()))
+        if own_W:
+            torch.cuda.current_stream().synchronize()      # W may be freed after return
+    return out
+
+
+def device_scenarios_keyed(meal_minute, meal_grams, start_minute, horizon_minutes, key, seed=0, mask=None):
+    """Rewrite columns of the meal table (meal_minute / meal_grams [M, E]) in place: RandomScenario-distributed meals
+    of an episode that starts at minute-of-day start_minute[e] (int32 device tensor); stream key[e], columns mask[e]."""
+    import torch
+    from . import _capi
+    lib = _capi.load()
+    assert meal_minute.is_contiguous() and meal_grams.is_contiguous() and start_minute.dtype == torch.int32
+    with torch.cuda.device(meal_minute.device):
+        _capi.check(lib.sg_gen_scenarios_keyed(C.c_void_p(meal_minute.data_ptr()), C.c_void_p(meal_grams.data_ptr()),
+                                               meal_minute.shape[1], meal_minute.shape[0],
+                                               C.c_void_p(start_minute.data_ptr()), int(horizon_minutes), seed,
+                                               C.c_void_p(key.data_ptr()),
+                                               C.c_void_p(mask.data_ptr()) if mask is not None else None, _stream()))
+    return meal_minute, meal_grams
+
+
+def device_episode_starts(key, patient_row=None, table_x0=None, n_draws=2, seed=0, mask=None, start_minute=None, x0=None):
+    """Start hour and randomised initial state of every episode with mask[e] != 0, as the gym wrapper draws them
+    (simglucose_gym_env.py:58-73; sg_gen_episode_starts).  start_minute [E] int32 / x0 [13, E] are written in place
+    (allocated when None and wanted: x0 is produced when patient_row is given).  Returns (start_minute, x0)."""
+    import torch
+    from . import _capi
+    lib = _capi.load()
+    dev = key.device
+    n = key.numel()
+    if start_minute is None:
+        start_minute = torch.zeros(n, dtype=torch.int32, device=dev)
+    if x0 is None and patient_row is not None:
+        x0 = torch.zeros(13, n, dtype=torch.float64, device=dev)
+    tx = None
+    if x0 is not None:
+        tx = table_x0 if table_x0 is not None else torch.from_numpy(P.cohort_table()[1]).to(dev)
+        assert tx.is_contiguous() and patient_row.dtype == torch.int32
+    with torch.cuda.device(dev):
+        _capi.check(lib.sg_gen_episode_starts(C.c_void_p(start_minute.data_ptr()),
+                                              C.c_void_p(x0.data_ptr()) if x0 is not None else None,
+                                              C.c_void_p(tx.data_ptr()) if tx is not None else None,
+                                              C.c_void_p(patient_row.data_ptr()) if patient_row is not None else None,
+                                              n, int(n_draws), seed, C.c_void_p(key.data_ptr()),
+                                              C.c_void_p(mask.data_ptr()) if mask is not None else None, _stream()))
+        if table_x0 is None and tx is not None:
+            torch.cuda.current_stream().synchronize()
+    return start_minute, x0
+
+
 def device_perturbed_params(patient_row, amplitude=0.1, seed=1234, episode_offset=0, table=None):
     """[32, E] device tensor: table[row] * (1 + amplitude * U(-1, 1)) per parameter (configs[3])."""
     import torch

@@ -13,7 +13,11 @@ from helpers import O
 
 pytestmark = pytest.mark.gpu
 
-TOL = H.REL_TOL
+TOL = H.REL_TOL          # the north-star contract: 1e-6
+# What the strict FP64 path actually delivers against the reference (measured 2e-13 .. 3e-11 over days; the kernel's exp /
+# log / pow are within 1 ulp of libm and every accept / reject decision of DOPRI5 is the reference's): asserted beside
+# the contract so that a regression of several orders of magnitude cannot hide under it.
+MEASURED = 1e-9
 
 
 def _engine(n, **kw):
@@ -50,23 +54,30 @@ def _col(res, name):
     return res['trace'][:, _capi.TRACE_COLS.index(name), :].T      # [E, n_steps+1]
 
 
-def _check_against_reference(d, idx, res, tol=TOL):
+def _check_against_reference(d, idx, res, tol=TOL, strict=True):
     """Golden columns recorded from the reference.  CHO / insulin of reference row r describe the step
-    r -> r+1 (env.py:88-97); the library stores them on the row the step produced."""
+    r -> r+1 (env.py:88-97); the library stores them on the row the step produced.
+    strict: the default arithmetic (no FMA contraction) is also held to the measured level; SG_FLAG_FMA, whose step
+    decisions may differ from scipy's, only to the contract."""
     idx = list(idx)
     for name in ('BG', 'CGM', 'LBGI', 'HBGI', 'Risk'):
         got, ref = _col(res, name), d[name][idx]
         if name in ('BG', 'CGM'):
             assert H.rel_err(got, ref) <= tol, name
+            if strict:
+                assert H.rel_err(got, ref) <= MEASURED, (name, H.rel_err(got, ref))
         else:
-            assert H.rel_err(got, ref) <= 2e-5, name       # risk is ~20x steeper than BG around 110 mg/dL
+            # risk is ~20x steeper than BG around 110 mg/dL: 1e-8 is the bound the oracle holds (test_oracle_golden.py)
+            assert H.rel_err(got, ref) <= (1e-8 if strict else 2e-5), (name, H.rel_err(got, ref))
     cho, ins = _col(res, 'CHO')[:, 1:], _col(res, 'insulin')[:, 1:]
     assert np.array_equal(cho, d['CHO'][idx][:, :-1]), 'announced CHO per step must be exact'
     assert np.max(np.abs(ins - d['insulin'][idx][:, :-1])) <= 1e-15, 'pump-quantised insulin'
-    assert H.rel_err(_col(res, 'obs'), d['obs'][idx]) <= tol
+    assert H.rel_err(_col(res, 'obs'), d['obs'][idx]) <= (MEASURED if strict else tol)
+    if 'reward' in d.files:
+        assert H.rel_err(_col(res, 'reward'), d['reward'][idx]) <= (1e-8 if strict else 1e-4)
     assert np.array_equal(_col(res, 'done') != 0, d['done'][idx])
     assert np.all(res['status'] == 1)
-    assert H.rel_err(res['state'].T, d['final_state'][idx]) <= tol
+    assert H.rel_err(res['state'].T, d['final_state'][idx]) <= (MEASURED if strict else tol)
 
 
 def test_golden_config_matches_sim_results_csv():
@@ -124,7 +135,7 @@ def test_oracle_bitwise_integer_work_and_stats():
     for i in range(n):
         o = H.oracle_episode(d, i)
         assert H.rel_err(_col(res, 'BG')[i], o['BG']) <= 1e-9
-        assert H.rel_err(_col(res, 'reward')[i], o['reward']) <= 1e-6
+        assert H.rel_err(_col(res, 'reward')[i], o['reward']) <= 1e-9
         assert np.array_equal(res['counters'][:, 0, i], o['counters'][:, 1])
         st = dict(zip(O.STAT_COLS, res['stats'][:, i]))
         for k in ('rows', 'lt50', 'lt70', 'inrange', 'gt180', 'gt250', 'first_done', 'dopri_steps', 'dopri_rejects'):
@@ -159,7 +170,7 @@ def test_fma_mode_within_tolerance():
     """SG_FLAG_FMA (contraction allowed) stays inside the FP64 tolerance on the 3-day cohort."""
     d = H.load('cohort_bb_3day')
     res = _run_fixture(d, range(30), fma=True)
-    _check_against_reference(d, range(30), res)
+    _check_against_reference(d, range(30), res, strict=False)
 
 
 def test_missing_noise_is_an_error():

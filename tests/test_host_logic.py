@@ -169,7 +169,7 @@ def test_controller_host_policies():
     assert bb.policy(Obs(CGM=120.0), 0, False, patient_name='adolescent#001', meal=3.0, sample_time=3).bolus == 9.0 / cr / 3
     unk = bb.policy(Obs(CGM=100.0), 0, False, patient_name='someone', meal=0, sample_time=3)
     assert unk.basal == 1.43 * 57.0 / 6000 and bb.device_spec('someone') is None
-    assert bb.device_spec('adolescent#001') == ('bb', (140.0, cr, cf, 0.0))
+    assert bb.device_spec('adolescent#001') == ('bb', (140.0, cr, cf, p[1] * p[0] / 6000))
     pid = PIDController(P=0.001, I=0.00001, D=0.001, target=140)
     a1 = pid.policy(Obs(CGM=150.0), 0, False, sample_time=3)
     assert a1.basal == 0.001 * 10.0 + 0.00001 * 0 + 0.001 * 150.0 / 3 and a1.bolus == 0      # derivative kick
