@@ -733,7 +733,7 @@ def main():
         if world > 1:
             dist.all_reduce(t3, op=dist.ReduceOp.MAX)
         configs['configs[3]'] = {
-            'config': 'configs[3] reduced: 262,144 episodes with +-10 % perturbed parameters x 1 day, BBController, '
+            'config': 'configs[3] reduced: 262,144 episodes with +-10 %% perturbed parameters x 1 day, BBController, '
                       'independent streams, sharded over %d GPU(s) (shard_range), distributed.allreduce_stats inside '
                       'the timed region; full size (16,777,216 x 7 days): bench.py --config 3, profiles/' % world,
             'value': 262144 * 1440 / float(t3.item()), 'unit': METRIC, 'seconds': float(t3.item()), 'n_gpus': world,

@@ -15,8 +15,12 @@ import sys
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, 'csrc')
 LIB_DIR = os.path.join(_HERE, 'lib')
-LIB_PATH = os.path.join(LIB_DIR, 'libsimglucose_b200.so')
-OBJ_DIR = os.path.join(LIB_DIR, 'obj')
+# A/B builds (tools/ab_variants.sh): SG_LIB_PATH names another output library, SG_NVCC_EXTRA adds compile flags
+# (e.g. -DSG_EXP_TABLE=0); the product always loads the default path.
+LIB_PATH = os.environ.get('SG_LIB_PATH') or os.path.join(LIB_DIR, 'libsimglucose_b200.so')
+OBJ_DIR = os.path.join(LIB_DIR, 'obj' if not os.environ.get('SG_LIB_PATH') else
+                       'obj_' + os.path.splitext(os.path.basename(LIB_PATH))[0])
+EXTRA = os.environ.get('SG_NVCC_EXTRA', '').split()
 
 ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
 COMMON = ['-O3', '-std=c++17', '-lineinfo', '-Xcompiler', '-fPIC', '-Xptxas', '-v']
@@ -66,7 +70,7 @@ def build(force=False, verbose=False):
         if not os.path.exists(srcp):
             continue
         out = os.path.join(OBJ_DIR, obj)
-        cmd = [nvcc] + ARCH + COMMON + extra + ['-c', srcp, '-o', out]
+        cmd = [nvcc] + ARCH + COMMON + extra + EXTRA + ['-c', srcp, '-o', out]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(out)
     for cmd, p in procs:
@@ -79,7 +83,7 @@ def build(force=False, verbose=False):
     log.append(' '.join(cmd) + '\n' + r.stdout)
     if r.returncode != 0:
         raise RuntimeError('link failed:\n' + log[-1])
-    with open(os.path.join(LIB_DIR, 'build.log'), 'w') as f:
+    with open(os.path.join(LIB_DIR, 'build.log' if not os.environ.get('SG_LIB_PATH') else os.path.basename(LIB_PATH) + '.log'), 'w') as f:
         f.write('\n'.join(log))
     if verbose:
         print('\n'.join(log))

@@ -214,6 +214,9 @@ static int sort_episodes(sg_handle h, cudaStream_t stream)
     sgc::SortArgs sa{};
     sa.n = h->n; sa.cap = h->cap; sa.sd = h->sd; sa.si = h->si;
     sa.meal_minute = h->meal_minute; sa.meal_grams = h->meal_grams; sa.max_meals = h->max_meals;
+    sa.patient_row = h->patient_row;
+    static const int sort_mode = getenv("SG_SORT_MODE") ? atoi(getenv("SG_SORT_MODE")) : 0;    // experiment knob
+    sa.mode = sort_mode;
     sa.window = h->coherence_steps * h->hw.st;
     sa.n_keys = h->sort_n_keys;
     sa.keys = h->sort_keys; sa.hist = h->sort_hist; sa.perm = h->perm;

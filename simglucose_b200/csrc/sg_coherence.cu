@@ -44,6 +44,7 @@ __global__ void __launch_bounds__(SBLOCK) key_hist_kernel(const SortArgs a)
         if (pos < a.max_meals && mm >= minute && mm - minute < a.window) {
             int g = (int)a.meal_grams[(int64_t)pos * a.n + e];
             g = g < 0 ? 0 : (g > GRAM_BUCKETS - 1 ? GRAM_BUCKETS - 1 : g);
+            if (a.mode == 1 && a.patient_row) g = (a.patient_row[e] & 31) * 4 + (g >> 5);   // same patient first
             key = (mm - minute + 1) * GRAM_BUCKETS + g;
         }
     }

@@ -69,6 +69,49 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
     }
 }
 
+// The same streams for a FEW episodes of a large population (a vector environment restarting the episodes that ended
+// in this env-step: mask[e] != 0 for well under 1 % of them).  One thread per episode would leave 31 lanes of a warp idle
+// behind a lane that writes ~480 samples 8 * n bytes apart; here a warp looks at its 32 episodes, and for every masked one
+// the 32 lanes compute the samples of a window together (the knots of the AR chain are recomputed by every lane from the
+// same Philox stream: ten normals per 150 minutes).  Bit-identical to noise_kernel for the same stream.
+__global__ void __launch_bounds__(128) noise_masked_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
+                                                          const double *W, double pacf, double gamma, double lambda,
+                                                          double delta, double xi, uint64_t seed, const StreamSel sel)
+{
+    extern __shared__ double sW[];
+    for (int i = threadIdx.x; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane;      // first episode of this warp
+    const int64_t mine = e0 + lane;
+    unsigned todo = __ballot_sync(0xffffffffu, mine < n && !sel.skip(mine));
+    while (todo) {
+        const int b = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int64_t e = e0 + b;
+        Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
+        double ar = rng.normal();
+        double knots[11];
+        knots[10] = xi + lambda * sinh((ar - gamma) / delta);
+        for (int64_t base = 0; base < n_noise; base += nsample - 1) {
+            knots[0] = knots[10];
+#pragma unroll
+            for (int k = 1; k <= 10; k++) {
+                ar = pacf * (ar + rng.normal());
+                knots[k] = xi + lambda * sinh((ar - gamma) / delta);
+            }
+            for (int r = 1 + lane; r < nsample; r += 32) {
+                const int64_t pos = base + r - 1;
+                if (pos >= n_noise) break;
+                double v = 0.0;
+#pragma unroll
+                for (int k = 0; k < 11; k++) v += sW[r * 11 + k] * knots[k];
+                out[pos * n + e] = v;
+            }
+        }
+    }
+}
+
 // RandomScenario: one schedule per calendar day, six candidate meals (scenario_gen.py:38-58).
 __global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, double *meal_grams, int64_t n,
                                                       int max_meals, int start_minute_all, const int32_t *start_minute_rows,
@@ -187,9 +230,15 @@ int sg_gen_noise_keyed(double *out, int64_t n_episodes, int64_t n_noise, int32_t
 {
     if (!out || !W_dev || !model_host || !key || n_episodes <= 0 || n_noise <= 0 || nsample < 2 || nsample * 11 > MAX_W)
         return SG_ERR_ARG;
-    noise_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
-        out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
-        model_host[4], seed, StreamSel{0, 1, key, mask});
+    const StreamSel sel{0, 1, key, mask};
+    if (mask)       // a few columns of a resident buffer: warp-cooperative
+        noise_masked_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+            out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
+            model_host[4], seed, sel);
+    else
+        noise_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+            out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
+            model_host[4], seed, sel);
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 

@@ -164,6 +164,8 @@ struct SortArgs {
     const int32_t *meal_minute;    // [max_meals][n]
     const double *meal_grams;
     int32_t max_meals;
+    const int32_t *patient_row;    // [n] or null
+    int32_t mode;                  // 0: key (minute, grams); 1: key (minute, patient row, grams / 8)
     int32_t window;                // minutes ahead that are told apart (the segment until the next sort)
     int32_t n_keys;                // key_count(window)
     int32_t *keys;                 // [cap] scratch

@@ -121,7 +121,8 @@ struct Minute {
     double d;      // action.CHO * 1000                      t1dpatient.py:121
     double ins;    // action.insulin * 6000 / BW             t1dpatient.py:122
     bool fed;      // Dbar > 0                               t1dpatient.py:130,135
-    double2 ab, cd;  // (aa, b*Dbar), (cc, d*Dbar) of the gastric-emptying law: the head of the RHS's longest chain, in registers
+    double2 ab, cd;  // (2 aa, b*Dbar), (2 cc, d*Dbar) of the gastric-emptying law: the head of the RHS's longest chain, in
+                     // registers; the slopes carry the factor 2 of tanh(u) = 1 - 2 / (e^2u + 1) (exact: a power of two)
 };
 
 // ins_per_kg: action.insulin * 6000 / BW (constant over an env-step: the caller divides once).
@@ -144,6 +145,7 @@ __device__ __forceinline__ Minute minute_setup_rate(const Column<BLOCK> &c, doub
         c.set(H_dD, c(H_d) * Dbar);
     }
     m.ab = c.pair(H_aa); m.cd = c.pair(H_cc);
+    m.ab.x *= 2.0; m.cd.x *= 2.0;
     return m;
 }
 
@@ -163,6 +165,7 @@ __device__ __forceinline__ Minute minute_setup(const Column<BLOCK> &c, double ch
         c.set(H_dD, c(H_d) * Dbar);
     }
     m.ab = c.pair(H_aa); m.cd = c.pair(H_cc);
+    m.ab.x *= 2.0; m.cd.x *= 2.0;
     return m;
 }
 
@@ -184,8 +187,8 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     dx[0] = -kmax * x[0] + m.d;                                             // :133
     // :135-142, branch-free: tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh),
     // evaluated for every lane and discarded by the select when Dbar == 0
-    const double2 ab = m.ab, cd = m.cd;                                     // (aa, b*Dbar), (cc, d*Dbar)
-    const double tdiff = sgm::tanh_diff(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
+    const double2 ab = m.ab, cd = m.cd;                                     // (2 aa, b*Dbar), (2 cc, d*Dbar)
+    const double tdiff = sgm::tanh_diff2(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
     const double2 kh = c.pair(H_kmin);                                      // kmin, (kmax - kmin) / 2
     const double kfed = kh.x + kh.y * (tdiff + 2.0);
     const double kgut = m.fed ? kfed : kmax;
@@ -442,7 +445,7 @@ __device__ __noinline__ double hinit_second(double *col, double h, double dnf, d
     return fmin(fmin(100.0 * fabs(h), h1), hmax);
 }
 
-struct StepControl { double err, hnew_accept, hnew_reject, lerr; };
+struct StepControl { double err, hnew_accept, hnew_reject, lerr; };   // hnew_reject: SG_MERGED_POW == 0 only
 
 // Step-size controller of DOPCOR (Lund stabilisation, beta = 0.04) from the summed squared scaled errors.
 // lfacold: log of facold (log_pos).  Returns the log of err as well: the caller keeps it as the next lfacold.
@@ -453,15 +456,33 @@ static __device__ __forceinline__ StepControl step_control(double errsum, double
     const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
     const double err = sqrt(sgm::div_nr(errsum, (double)NX));
     const double lerr = sgm::log_pos(err);
-    const double fac11 = sgm::pow_of_log(lerr, expo1);
-    double fac = sgm::div_nr(fac11, sgm::pow_of_log(lfacold, beta));
-    fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
     StepControl r;
     r.err = err;
     r.lerr = lerr;
+#if SG_MERGED_POW
+    // fac11 / facold^beta = err^expo1 / facold^beta with ONE exp: exp(expo1 ln err - beta ln facold).  The two powers are
+    // transcendental results defined to an ulp each, and so is their quotient; everything around it stays exact
+    // arithmetic.  The rejected-step formula needs err^expo1 alone: step_reject, on the (rare) rejected steps only.
+    double fac = sgm::exp_core(expo1 * lerr - beta * lfacold);
+    fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
+    r.hnew_accept = sgm::div_nr(h, fac);
+    r.hnew_reject = 0.0;
+#else
+    const double fac11 = sgm::pow_of_log(lerr, expo1);
+    double fac = sgm::div_nr(fac11, sgm::pow_of_log(lfacold, beta));
+    fac = sgm::max_sel(facc2, sgm::min_sel(facc1, sgm::div_nr(fac, safe)));
     r.hnew_accept = sgm::div_nr(h, fac);
     r.hnew_reject = sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
+#endif
     return r;
+}
+
+// hnew after a rejected step: h / min(facc1, err^expo1 / safe) (DOPCOR).
+static __device__ __noinline__ double step_reject(double lerr, double h)
+{
+    const double expo1 = 0.2 - 0.04 * 0.75, safe = 0.9, facc1 = 1.0 / 0.2;
+    const double fac11 = sgm::pow_of_log(lerr, expo1);
+    return sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
 }
 
 // One call of ode('dopri5').integrate(t + 1): k1 = f(y), HINIT (initial step size guess) unless a step
@@ -665,7 +686,11 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                     begin_step = true;
                 }
             } else {
+#if SG_MERGED_POW
+                hnew = step_reject(sc.lerr, h);
+#else
                 hnew = sc.hnew_reject;
+#endif
                 reject = true;
                 if (naccpt >= 1) cnt.nrej++;
                 last = false;

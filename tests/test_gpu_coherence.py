@@ -222,7 +222,8 @@ def test_bb_basal_by_name_for_perturbed_rows():
     eng.reset(rows, noise, mm, mg, params=pp, row0=False)
     own_tr = eng.run(n_steps, controller='bb', ctrl_rows=own, trace=True)['trace']
     assert torch.equal(named[:, T('basal')], ctrl_rows[3].expand(n_steps, E))
-    want_own = (pp[1] * pp[0] / 6000.0).expand(n_steps, E)
+    pph = pp.cpu().numpy()                                  # numpy: a true division (torch multiplies by 1 / 6000 on CUDA)
+    want_own = torch.from_numpy(pph[1] * pph[0] / 6000.0).to(pp.device).expand(n_steps, E)
     assert torch.equal(own_tr[:, T('basal')], want_own) and not torch.equal(named[:, T('basal')], own_tr[:, T('basal')])
     # unperturbed rows: both conventions coincide bit for bit
     eng.reset(rows, noise, mm, mg, row0=False)

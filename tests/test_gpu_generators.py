@@ -58,6 +58,16 @@ def test_device_noise_matches_cgmnoise_distribution(sensor):
     assert abs(np.corrcoef(dev[0::2, 40], dev[1::2, 40])[0, 1]) < 5 / np.sqrt(E_dev / 2)
     grp = S.device_noise(60, L, sensor, seed=7, group_size=30).cpu().numpy()
     assert np.array_equal(grp[:, :30], np.repeat(grp[:, :1], 30, 1)) and not np.array_equal(grp[:, 0], grp[:, 30])
+    # keyed streams: the warp-cooperative kernel that rewrites a few masked columns of a resident buffer gives the same
+    # bits as the one-thread-per-episode kernel, and leaves the other columns alone
+    key = torch.arange(1000, device='cuda', dtype=torch.int64) * 3 + 11
+    full = S.device_noise_keyed(torch.zeros(L + 3, 1000, dtype=torch.float64, device='cuda'), key, sensor, seed=3)
+    mask = (torch.arange(1000, device='cuda') % 7 == 2).to(torch.int32)
+    part = S.device_noise_keyed(torch.full((L + 3, 1000), -1.0, dtype=torch.float64, device='cuda'), key, sensor, seed=3, mask=mask)
+    m = mask.bool()
+    assert torch.equal(part[:, m], full[:, m]) and bool((part[:, ~m] == -1.0).all())
+    ones = torch.ones(1000, dtype=torch.int32, device='cuda')
+    assert torch.equal(S.device_noise_keyed(torch.zeros_like(full), key, sensor, seed=3, mask=ones), full)
 
 
 _PROB = [0.95, 0.3, 0.95, 0.3, 0.95, 0.3]                   # scenario_gen.py:38-44

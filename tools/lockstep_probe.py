@@ -1,31 +1,43 @@
-import sys, time, torch
+"""Where a lockstep env-step of the vector environment spends its time (configs[2]): CUDA-event timing of
+  (a) the bare step kernel loop (engine.run(1, 'random')), (b) T1DSimVecEnv.step_random without resets,
+  (c) with gym seeding + per-environment resets; run under `ncu --metrics gpu__time_duration.sum` for the launch list.
+    python tools/lockstep_probe.py [envs] [steps] [mode]"""
+import sys
+import time
+
+import torch
+
 sys.path.insert(0, '/root/repo')
-from simglucose_b200 import streams as S
-from simglucose_b200.engine import BatchEngine
-E, n_steps = 1048576, 60
-dev = torch.device('cuda', 0)
-import itertools
-for group, cap in itertools.product((1, 30), (0, 5, 8)):
-    rows = (torch.arange(E, device=dev, dtype=torch.int64) % 30).to(torch.int32)
-    noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=3, group_size=group, device=dev)
-    mm, mg = S.device_scenarios(E, n_steps * 3, start_minute=6*60, seed=3, group_size=group, device=dev)
-    acts = torch.stack([S.device_uniform(E, 0.0, 0.05, seed=0, offset=k * E) for k in range(n_steps)])
-    zeros = torch.zeros(E, dtype=torch.float64, device=dev)
-    full = torch.stack([acts, torch.zeros_like(acts)], dim=1).contiguous()
-    eng = BatchEngine(E)
-    eng.set_step_cap(cap)
-    def fused():
-        eng.reset(rows, noise, mm, mg, row0=False)
-        eng.run(n_steps, controller='actions', actions=full, trace=False)
-    out = eng.empty(12)
-    def lock():
-        eng.reset(rows, noise, mm, mg, row0=False)
-        for k in range(n_steps):
-            eng.step(acts[k], zeros, out=out)
-    for name, fn in (('fused', fused), ('lockstep', lock)):
-        fn(); torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter(); e0.record(); fn(); e1.record(); t1 = time.perf_counter(); torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1)
-        print('cap %d group %d %-9s %.1f ms  (%.3f ms/env-step, %.3g patient-min/s)  host launch time %.1f ms' % (cap, group, name, ms, ms / n_steps, E * n_steps * 3 / ms * 1e3, (t1 - t0) * 1e3))
-    eng.close()
+from simglucose_b200.envs import T1DSimVecEnv  # noqa: E402
+
+E = int(sys.argv[1]) if len(sys.argv) > 1 else 1048576
+n_steps = int(sys.argv[2]) if len(sys.argv) > 2 else 60
+modes = sys.argv[3].split(',') if len(sys.argv) > 3 else ['kernel', 'plain', 'gym']
+
+
+def timed(fn):
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter(); e0.record(); fn(); e1.record(); t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1), (t1 - t0) * 1e3
+
+
+for mode in modes:
+    gym = mode == 'gym'
+    env = T1DSimVecEnv(E, seed=0, horizon_steps=480, gym_seeding=gym, auto_reset=gym)
+    env.reset()
+    for _ in range(45):                                   # past the first sort and the first resets
+        env.step_random(0.0, 0.05)
+    if mode == 'kernel':
+        def loop():
+            for _ in range(n_steps):
+                env.engine.run(1, controller='random', ctrl=(0.0, 0.05, 0.0, 0.0), trace=env._row)
+    else:
+        def loop():
+            for _ in range(n_steps):
+                env.step_random(0.0, 0.05)
+    ms, host = timed(loop)
+    print('%-6s %d envs: %.3f ms per env-step on the device, %.3f ms of host time per step, %.3g patient-min/s'
+          % (mode, E, ms / n_steps, host / n_steps, E * n_steps * 3 / ms * 1e3), flush=True)
+    env.close()
