@@ -209,3 +209,49 @@ def test_run_shards_streams_host_population_identically():
         assert agg[k] == agg_want[k]
     for k in (1, 4, 5, 6, 7):
         assert abs(agg[k] - agg_want[k]) <= 1e-9 * max(1.0, abs(agg_want[k]))
+
+
+def test_config3_shard_halves_reduce_to_the_single_engine_aggregate():
+    """The multi-GPU claim of configs[3] on one GPU: a 2^18-episode perturbed population (parameters and streams
+    generated on device, keyed by GLOBAL episode index) simulated as ONE batch and as the two contiguous halves
+    distributed.shard_range(E, r, 2) gives the two ranks.  Per-episode statistics are bit-identical (an episode does
+    not know its shard), the counters of the aggregate are bitwise equal, the floating-point sums agree to 1e-12
+    relative (only their summation order differs), min / max exactly."""
+    import torch
+    import bench
+    from simglucose_b200 import _capi, streams as S
+    from simglucose_b200.distributed import shard_range
+    from simglucose_b200.engine import BatchEngine
+    E, n_steps, seed = 262144, 96, 1234
+    dev = torch.device('cuda', 0)
+
+    def run(lo, hi):
+        n = hi - lo
+        rows = ((torch.arange(n, device=dev, dtype=torch.int64) + lo) % 30).to(torch.int32)
+        pp = S.device_perturbed_params(rows, amplitude=0.1, seed=seed, episode_offset=lo)
+        noise = S.device_noise(n, n_steps + 2, 'Dexcom', seed=seed, episode_offset=lo, group_size=1, device=dev)
+        mm, mg = S.device_scenarios(n, n_steps * 3, start_minute=7 * 60, seed=seed, episode_offset=lo, group_size=1, device=dev)
+        eng = BatchEngine(n, coherence=40)
+        eng.reset(rows, noise, mm, mg, params=pp, row0=False)
+        eng.run(n_steps, controller='bb', ctrl_rows=bench.controller_rows_device(rows), trace=False)
+        assert int((eng.status() != 1).sum()) == 0
+        st, agg = eng.stats().clone(), eng.reduce_stats().clone()
+        eng.close()
+        return st, agg, mm.shape[0]
+
+    whole, agg_whole, _ = run(0, E)
+    halves = [run(*shard_range(E, r, 2)) for r in range(2)]
+    assert shard_range(E, 0, 2) == (0, E // 2) and shard_range(E, 1, 2) == (E // 2, E)
+    assert torch.equal(torch.cat([h[0] for h in halves], dim=1), whole)
+    a, b, w = halves[0][1].cpu().numpy(), halves[1][1].cpu().numpy(), agg_whole.cpu().numpy()
+    names = _capi.STAT_COLS
+    for k, name in enumerate(names):
+        if name == 'min_bg':
+            assert min(a[k], b[k]) == w[k]
+        elif name == 'max_bg':
+            assert max(a[k], b[k]) == w[k]
+        elif name in ('rows', 'lt50', 'lt70', 'inrange', 'gt180', 'gt250', 'first_done', 'dopri_steps', 'dopri_rejects'):
+            assert a[k] + b[k] == w[k], name                      # integer-valued doubles: exact in any order
+        else:
+            assert abs(a[k] + b[k] - w[k]) <= 1e-12 * max(1.0, abs(w[k])), name
+    assert w[names.index('rows')] == E * (n_steps + 1)
