@@ -71,43 +71,92 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
 
 // The same streams for a FEW episodes of a large population (a vector environment restarting the episodes that ended
 // in this env-step: mask[e] != 0 for well under 1 % of them).  One thread per episode would leave 31 lanes of a warp idle
-// behind a lane that writes ~480 samples 8 * n bytes apart; here a warp looks at its 32 episodes, and for every masked one
-// the 32 lanes compute the samples of a window together (the knots of the AR chain are recomputed by every lane from the
-// same Philox stream: ten normals per 150 minutes).  Bit-identical to noise_kernel for the same stream.
-__global__ void __launch_bounds__(128) noise_masked_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
-                                                          const double *W, double pacf, double gamma, double lambda,
-                                                          double delta, double xi, uint64_t seed, const StreamSel sel)
+// behind a lane that walks ~1000 normal deviates and writes ~480 samples 8 * n bytes apart.  Here a block of four warps
+// looks at its 128 episodes, lists the masked ones, and every warp takes listed episodes in turn; for one episode the 32
+// lanes own one 15-minute window each (32 windows per round):
+//   1. lane w draws the ten deviates of window w by random access into the Philox stream (Philox::block_at) -- the
+//      expensive part, 32 windows at a time;
+//   2. the AR chain ar <- pacf * (ar + z) is a serial recurrence: every lane walks the round's 320 deviates from shared
+//      memory (two dependent FP64 operations per deviate) and lane (index mod 32) stores each value;
+//   3. lane w transforms its eleven knots and interpolates the samples of its window.
+// Same deviates, same chain, same expressions as noise_kernel: bit-identical streams (tests/test_gpu_generators.py).
+constexpr int NM_WARPS = 4;
+
+__global__ void __launch_bounds__(32 * NM_WARPS) noise_masked_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
+                                                                    const double *W, double pacf, double gamma,
+                                                                    double lambda, double delta, double xi, uint64_t seed,
+                                                                    const StreamSel sel)
 {
-    extern __shared__ double sW[];
+    extern __shared__ double sW[];                         // nsample * 11 interpolation weights
+    __shared__ double zs[NM_WARPS][320];                   // deviates of a round
+    __shared__ double as[NM_WARPS][320];                   // chain values of a round
+    __shared__ int list[32 * NM_WARPS];
+    __shared__ int n_list;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t mine = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (threadIdx.x == 0) n_list = 0;
+    __syncthreads();
+    const bool sel_me = mine < n && !sel.skip(mine);
+    const unsigned ballot = __ballot_sync(0xffffffffu, sel_me);
+    int base_slot = 0;
+    if (lane == 0 && ballot) base_slot = atomicAdd(&n_list, __popc(ballot));
+    base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
+    if (sel_me) list[base_slot + __popc(ballot & ((1u << lane) - 1u))] = threadIdx.x;
+    __syncthreads();
+    const int count = n_list;
+    if (count == 0) return;
     for (int i = threadIdx.x; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const int64_t e0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane;      // first episode of this warp
-    const int64_t mine = e0 + lane;
-    unsigned todo = __ballot_sync(0xffffffffu, mine < n && !sel.skip(mine));
-    while (todo) {
-        const int b = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const int64_t e = e0 + b;
-        Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
-        double ar = rng.normal();
-        double knots[11];
-        knots[10] = xi + lambda * sinh((ar - gamma) / delta);
-        for (int64_t base = 0; base < n_noise; base += nsample - 1) {
-            knots[0] = knots[10];
+    const int per_window = nsample - 1;
+    const int64_t n_windows = (n_noise + per_window - 1) / per_window;
+    double *z = zs[warp], *av = as[warp];
+    for (int li = warp; li < count; li += NM_WARPS) {
+        const int64_t e = (int64_t)blockIdx.x * blockDim.x + list[li];
+        const Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
+        uint32_t w4[4];
+        rng.block_at(0, w4);
+        double ar = Philox::normal_of(w4, 0);               // deviate 0: _noise_init, noise_gen.py:84-85
+        for (int64_t w0 = 0; w0 < n_windows; w0 += 32) {
+            const int64_t win = w0 + lane;
+            const int n_round = (int)min((int64_t)32, n_windows - w0) * 10;     // deviates of this round
+            if (win < n_windows) {
+                // deviates 1 + 10 win .. 10 + 10 win: an odd first index, i.e. the second half of one draw block, four
+                // whole blocks, the first half of a sixth
+                const uint32_t b0 = (uint32_t)((1 + 10 * win) >> 1);
+                rng.block_at(b0, w4);
+                z[lane * 10 + 0] = Philox::normal_of(w4, 1);
 #pragma unroll
-            for (int k = 1; k <= 10; k++) {
-                ar = pacf * (ar + rng.normal());
-                knots[k] = xi + lambda * sinh((ar - gamma) / delta);
+                for (int b = 1; b <= 4; b++) {
+                    rng.block_at(b0 + b, w4);
+                    z[lane * 10 + 2 * b - 1] = Philox::normal_of(w4, 0);
+                    z[lane * 10 + 2 * b] = Philox::normal_of(w4, 1);
+                }
+                rng.block_at(b0 + 5, w4);
+                z[lane * 10 + 9] = Philox::normal_of(w4, 0);
             }
-            for (int r = 1 + lane; r < nsample; r += 32) {
-                const int64_t pos = base + r - 1;
-                if (pos >= n_noise) break;
-                double v = 0.0;
+            __syncwarp();
+            const double ar_in = ar;                        // chain value before this round
+            for (int j = 0; j < n_round; j++) {
+                ar = pacf * (ar + z[j]);                    // noise_gen.py:86-88
+                if ((j & 31) == lane) av[j] = ar;
+            }
+            __syncwarp();
+            if (win < n_windows) {
+                double knots[11];
+                const double a0 = lane == 0 ? ar_in : av[lane * 10 - 1];
+                knots[0] = xi + lambda * sinh((a0 - gamma) / delta);            // the knot carried over, noise_gen.py:33-36
 #pragma unroll
-                for (int k = 0; k < 11; k++) v += sW[r * 11 + k] * knots[k];
-                out[pos * n + e] = v;
+                for (int k = 1; k <= 10; k++) knots[k] = xi + lambda * sinh((av[lane * 10 + k - 1] - gamma) / delta);
+                for (int r = 1; r < nsample; r++) {
+                    const int64_t pos = win * per_window + r - 1;
+                    if (pos >= n_noise) break;
+                    double v = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 11; k++) v += sW[r * 11 + k] * knots[k];
+                    out[pos * n + e] = v;
+                }
             }
+            __syncwarp();
         }
     }
 }
@@ -232,7 +281,7 @@ int sg_gen_noise_keyed(double *out, int64_t n_episodes, int64_t n_noise, int32_t
         return SG_ERR_ARG;
     const StreamSel sel{0, 1, key, mask};
     if (mask)       // a few columns of a resident buffer: warp-cooperative
-        noise_masked_kernel<<<blocks(n_episodes, 128), 128, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+        noise_masked_kernel<<<blocks(n_episodes, 32 * NM_WARPS), 32 * NM_WARPS, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
             out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
             model_host[4], seed, sel);
     else

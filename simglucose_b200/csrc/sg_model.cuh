@@ -445,19 +445,42 @@ __device__ __noinline__ double hinit_second(double *col, double h, double dnf, d
     return fmin(fmin(100.0 * fabs(h), h1), hmax);
 }
 
-struct StepControl { double err, hnew_accept, hnew_reject, lerr; };   // hnew_reject: SG_MERGED_POW == 0 only
+#if SG_FAST_ERRNORM
+#define SG_ERR_QUOT(e, sk) ((e) * sgm::rcp_ulp(sk))
+#else
+#define SG_ERR_QUOT(e, sk) sgm::div_nr(e, sk)
+#endif
+
+struct StepControl { bool accept, above_floor; double hnew_accept, hnew_reject, lerr; };   // hnew_reject: SG_MERGED_POW == 0 only
 
 // Step-size controller of DOPCOR (Lund stabilisation, beta = 0.04) from the summed squared scaled errors.
 // lfacold: log of facold (log_pos).  Returns the log of err as well: the caller keeps it as the next lfacold.
+// accept = (err <= 1), above_floor = (err > 1e-4) with err = sqrt(errsum / 13).
 static __device__ __forceinline__ StepControl step_control(double errsum, double lfacold, double h)
 {
     const double beta = 0.04, safe = 0.9;
     const double expo1 = 0.2 - beta * 0.75;
     const double facc1 = 1.0 / 0.2, facc2 = 1.0 / 10.0;
+    StepControl r;
+#if SG_FAST_CONTROL
+    // err = sqrt(errsum / 13) is never formed: log(err) = (log(errsum) - log 13) / 2; the two comparisons of err are
+    // comparisons of errsum with the largest doubles x for which sqrt(fl(x / 13)) <= 1 resp. <= 1e-4 (found by
+    // bisection over the doubles; IEEE division and square root are monotone), so the decisions are those of DOPCOR
+    // bit for bit.  hnew = h / max(facc2, min(facc1, fac / safe)) = h * min(10, max(0.2, safe / fac)) with
+    // 1 / fac = facold^beta / err^expo1 = exp(beta ln facold - expo1 ln err): one exp, no division -- a
+    // transcendental result defined to an ulp like the powers it replaces.
+    const double lerr = 0.5 * (sgm::log_pos(errsum) - 0x1.485042b318c51p+1);
+    r.lerr = lerr;
+    r.accept = errsum <= 0x1.a000000000002p+3;
+    r.above_floor = errsum > 0x1.172c417c771f0p-23;
+    const double g = sgm::exp_core(beta * lfacold - expo1 * lerr);
+    r.hnew_accept = h * sgm::min_sel(10.0, sgm::max_sel(0.2, safe * g));
+    r.hnew_reject = 0.0;
+#else
     const double err = sqrt(sgm::div_nr(errsum, (double)NX));
     const double lerr = sgm::log_pos(err);
-    StepControl r;
-    r.err = err;
+    r.accept = err <= 1.0;
+    r.above_floor = err > 1.0e-4;
     r.lerr = lerr;
 #if SG_MERGED_POW
     // fac11 / facold^beta = err^expo1 / facold^beta with ONE exp: exp(expo1 ln err - beta ln facold).  The two powers are
@@ -474,6 +497,7 @@ static __device__ __forceinline__ StepControl step_control(double errsum, double
     r.hnew_accept = sgm::div_nr(h, fac);
     r.hnew_reject = sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
 #endif
+#endif
     return r;
 }
 
@@ -481,8 +505,12 @@ static __device__ __forceinline__ StepControl step_control(double errsum, double
 static __device__ __noinline__ double step_reject(double lerr, double h)
 {
     const double expo1 = 0.2 - 0.04 * 0.75, safe = 0.9, facc1 = 1.0 / 0.2;
+#if SG_FAST_CONTROL
+    return h * sgm::max_sel(0.2, safe * sgm::exp_core(-expo1 * lerr));       // h / min(5, err^expo1 / safe)
+#else
     const double fac11 = sgm::pow_of_log(lerr, expo1);
     return sgm::div_nr(h, sgm::min_sel(facc1, sgm::div_nr(fac11, safe)));
+#endif
 }
 
 // One call of ode('dopri5').integrate(t + 1): k1 = f(y), HINIT (initial step size guess) unless a step
@@ -653,27 +681,61 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             phase = PH_S7;
             } else {                                           // kt = k7 = f(x + h, y1): error estimate + control
             double err = 0.0;
+#if SG_FAST_ERRNORM == 2
+            // the 13 reciprocals advance together, one refinement level at a time: 13 independent chains for the
+            // scheduler instead of one quotient after the other (the sums P4..P6 are dead here, registers are free)
+            double sk[NX], rr[NX], ee[NX];
+            SG_FOR_PAIRS(i) {
+                const double2 y2 = yy[i / 2];
+                // max(|y|, |ynew|): select the operand, take the magnitude inside the product (an operand modifier)
+                sk[i] = ATOL + RTOL * fabs(fabs(y2.x) > fabs(yt[i]) ? y2.x : yt[i]);
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    sk[q] = ATOL + RTOL * fabs(fabs(y2.y) > fabs(yt[q]) ? y2.y : yt[q]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < NX; i++) rr[i] = sgm::rcp_seed(sk[i]);
+#pragma unroll
+            for (int i = 0; i < NX; i++) ee[i] = fma(rr[i], -sk[i], 1.0);
+#pragma unroll
+            for (int i = 0; i < NX; i++) ee[i] = fma(ee[i], ee[i], ee[i]);
+#pragma unroll
+            for (int i = 0; i < NX; i++) rr[i] = fma(rr[i], ee[i], rr[i]);
+            SG_FOR_PAIRS(i) {
+                const double2 pe = c.pair(H_PE + i);
+                {
+                    const double a = ((pe.x + E7 * kt[i]) * h) * rr[i];
+                    err = err + a * a;
+                }
+                if (i + 1 < NX) {
+                    const int q = i + 1 < NX ? i + 1 : i;
+                    const double a = ((pe.y + E7 * kt[q]) * h) * rr[q];
+                    err = err + a * a;
+                }
+            }
+#else
             SG_FOR_PAIRS(i) {
                 const double2 y2 = yy[i / 2], pe = c.pair(H_PE + i);
                 {
                     const double e = (pe.x + E7 * kt[i]) * h;
                     const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.x), fabs(yt[i]));
-                    const double a = sgm::div_nr(e, sk);
+                    const double a = SG_ERR_QUOT(e, sk);
                     err = err + a * a;
                 }
                 if (i + 1 < NX) {
                     const int q = i + 1 < NX ? i + 1 : i;
                     const double e = (pe.y + E7 * kt[q]) * h;
                     const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.y), fabs(yt[q]));
-                    const double a = sgm::div_nr(e, sk);
+                    const double a = SG_ERR_QUOT(e, sk);
                     err = err + a * a;
                 }
             }
+#endif
             const StepControl sc = step_control(err, lfacold, h);
-            err = sc.err;
             double hnew = sc.hnew_accept;
-            if (err <= 1.0) {
-                lfacold = (err > 1.0e-4) ? sc.lerr : c(H_L4);        // facold = max(err, 1e-4)
+            if (sc.accept) {
+                lfacold = sc.above_floor ? sc.lerr : c(H_L4);        // facold = max(err, 1e-4)
                 naccpt++;
                 store_vec(c, H_Y, yt);                       // kt is k1 of the next step (FSAL)
                 x = x + h;
