@@ -309,6 +309,21 @@ int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const i
                             int64_t n_episodes, double amplitude, uint64_t seed, int64_t episode_offset,
                             void *stream);
 
+/* Book-keeping of a lockstep vector environment around per-environment resets -- the `if done: env.reset()` of an RL loop
+ * over envs/simglucose_gym_env.py:48-51, for every environment at once (simglucose_b200/envs/vector_env.py).
+ * sg_vec_finish, after an env-step: episode_steps[e] += 1; done[e] = row[done_row][e] != 0 (env.py:103); mask[e] = done or
+ *   episode_steps[e] >= horizon_steps; truncated[e] = mask and not done; terminal_obs[e] = row[obs_row][e];
+ *   key[e] = ((env_offset + e) / group_size << key_shift) | episodes_started[e], the Philox stream of the episode that
+ *   would replace e (sg_gen_*_keyed).  row: the [SG_NTRACE][n_envs] history row of the step.
+ * sg_vec_restart, after sg_reset_masked(mask): episodes_started[e] += 1 and episode_steps[e] = 0 where mask[e] != 0;
+ *   obs_out[e] = mask[e] ? obs_new[e] : obs_step[e]. */
+int sg_vec_finish(const double *row, int64_t n_envs, int32_t done_row, int32_t obs_row, int32_t *episode_steps,
+                  int32_t horizon_steps, const int64_t *episodes_started, int64_t env_offset, int64_t group_size,
+                  int32_t key_shift, int32_t *mask, int64_t *key, double *terminal_obs, uint8_t *done, uint8_t *truncated,
+                  void *stream);
+int sg_vec_restart(const int32_t *mask, int64_t n_envs, int64_t *episodes_started, int32_t *episode_steps,
+                   const double *obs_new, const double *obs_step, double *obs_out, void *stream);
+
 /* out[i] ~ U(lo, hi): random basal actions (BASELINE.json configs[2]). */
 int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, uint64_t offset, void *stream);
 
@@ -329,7 +344,8 @@ int sg_cvga_zones(const double *cvga, int64_t n_episodes, double *counts_out, vo
 
 /* Accuracy probe of the kernel's own FP64 helpers (csrc/sg_math.cuh) against CUDA's libm, elementwise:
  * kind 0 div_nr(a,b), 1 a/b, 2 tanh_diff(a,b), 3 tanh(a)-tanh(b), 4 pow_pos(a,b), 5 pow(a,b), 6 exp_core(a),
- * 7 exp(a), 8 log_core(a), 9 log(a).  Test hook only. */
+ * 7 exp(a), 8 log_core(a), 9 log(a), 10 2 * tanh_sum_half(2a, 2b) (tanh(a) - tanh(b) + 2 as the RHS forms it),
+ * 11 tanh(a) - tanh(b) + 2, 12 rcp_ulp(a), 13 is_neg(a) + 2 * is_pos(a), 14 exp_tanh(a).  Test hook only. */
 int sg_math_probe(int32_t kind, const double *a, const double *b, double *out, int64_t n, void *stream);
 
 /* FP64 pipe probe: n_blocks x n_threads threads each run `iters` x 8 independent DFMA; out gets one double per

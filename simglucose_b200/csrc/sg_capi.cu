@@ -480,7 +480,7 @@ int sg_cgm_measure(const double *bg, const double *noise, double *out, int64_t n
 
 int sg_math_probe(int32_t kind, const double *a, const double *b, double *out, int64_t n, void *stream)
 {
-    if (kind < 0 || kind > 9 || !a || !b || !out || n <= 0) return fail(SG_ERR_ARG, "sg_math_probe: bad arguments");
+    if (kind < 0 || kind > 14 || !a || !b || !out || n <= 0) return fail(SG_ERR_ARG, "sg_math_probe: bad arguments");
     cudaError_t ce = sg_strict::launch_math_probe(kind, a, b, out, n, (cudaStream_t)stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_math_probe: launch", ce);
     return SG_OK;

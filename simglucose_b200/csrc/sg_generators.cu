@@ -39,6 +39,23 @@ struct StreamSel {
     }
 };
 
+// The arithmetic of one CGMNoise knot, written with rounding-explicit intrinsics: the file is compiled with FMA
+// contraction, and a contraction across these statements (pacf * (ar + z) - gamma as one fma) would make the value
+// depend on the shape of the surrounding code -- the two kernels below must agree bit for bit.  numpy evaluates the
+// same expressions without contraction (noise_gen.py:24, 86-88).
+__device__ __forceinline__ double ar_next(double pacf, double ar, double z) { return __dmul_rn(pacf, __dadd_rn(ar, z)); }
+__device__ __forceinline__ double johnson(double ar, double gamma, double lambda, double delta, double xi)
+{
+    return __dadd_rn(xi, __dmul_rn(lambda, sinh(__ddiv_rn(__dsub_rn(ar, gamma), delta))));
+}
+__device__ __forceinline__ double interp11(const double *w, const double (&knots)[11])
+{
+    double v = 0.0;
+#pragma unroll
+    for (int k = 0; k < 11; k++) v = fma(w[k], knots[k], v);
+    return v;
+}
+
 __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
                                                    const double *W, double pacf, double gamma, double lambda,
                                                    double delta, double xi, uint64_t seed, const StreamSel sel)
@@ -51,21 +68,17 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
     Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
     double ar = rng.normal();                                   // noise_gen.py:84-85
     double knots[11];
-    knots[10] = xi + lambda * sinh((ar - gamma) / delta);       // _noise_init, noise_gen.py:24
+    knots[10] = johnson(ar, gamma, lambda, delta, xi);          // _noise_init, noise_gen.py:24
     int64_t pos = 0;
     while (pos < n_noise) {
         knots[0] = knots[10];                                   // noise_gen.py:33-36
 #pragma unroll
         for (int k = 1; k <= 10; k++) {
-            ar = pacf * (ar + rng.normal());                    // noise_gen.py:86-88
-            knots[k] = xi + lambda * sinh((ar - gamma) / delta);
+            ar = ar_next(pacf, ar, rng.normal());               // noise_gen.py:86-88
+            knots[k] = johnson(ar, gamma, lambda, delta, xi);
         }
-        for (int r = 1; r < nsample && pos < n_noise; r++, pos++) {   // noise[1:], noise_gen.py:47
-            double v = 0.0;
-#pragma unroll
-            for (int k = 0; k < 11; k++) v += sW[r * 11 + k] * knots[k];
-            out[pos * n + e] = v;
-        }
+        for (int r = 1; r < nsample && pos < n_noise; r++, pos++)     // noise[1:], noise_gen.py:47
+            out[pos * n + e] = interp11(sW + r * 11, knots);
     }
 }
 
@@ -77,7 +90,7 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
 //   1. lane w draws the ten deviates of window w by random access into the Philox stream (Philox::block_at) -- the
 //      expensive part, 32 windows at a time;
 //   2. the AR chain ar <- pacf * (ar + z) is a serial recurrence: every lane walks the round's 320 deviates from shared
-//      memory (two dependent FP64 operations per deviate) and lane (index mod 32) stores each value;
+//      memory (two dependent FP64 operations per deviate) and lane w keeps the values of window w;
 //   3. lane w transforms its eleven knots and interpolates the samples of its window.
 // Same deviates, same chain, same expressions as noise_kernel: bit-identical streams (tests/test_gpu_generators.py).
 constexpr int NM_WARPS = 4;
@@ -89,7 +102,6 @@ __global__ void __launch_bounds__(32 * NM_WARPS) noise_masked_kernel(double *out
 {
     extern __shared__ double sW[];                         // nsample * 11 interpolation weights
     __shared__ double zs[NM_WARPS][320];                   // deviates of a round
-    __shared__ double as[NM_WARPS][320];                   // chain values of a round
     __shared__ int list[32 * NM_WARPS];
     __shared__ int n_list;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -109,7 +121,7 @@ __global__ void __launch_bounds__(32 * NM_WARPS) noise_masked_kernel(double *out
     __syncthreads();
     const int per_window = nsample - 1;
     const int64_t n_windows = (n_noise + per_window - 1) / per_window;
-    double *z = zs[warp], *av = as[warp];
+    double *z = zs[warp];
     for (int li = warp; li < count; li += NM_WARPS) {
         const int64_t e = (int64_t)blockIdx.x * blockDim.x + list[li];
         const Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
@@ -135,25 +147,33 @@ __global__ void __launch_bounds__(32 * NM_WARPS) noise_masked_kernel(double *out
                 z[lane * 10 + 9] = Philox::normal_of(w4, 0);
             }
             __syncwarp();
-            const double ar_in = ar;                        // chain value before this round
-            for (int j = 0; j < n_round; j++) {
-                ar = pacf * (ar + z[j]);                    // noise_gen.py:86-88
-                if ((j & 31) == lane) av[j] = ar;
+            // the chain, window by window: every lane computes every value (two dependent FP64 operations per deviate,
+            // the loads run ahead), lane w keeps the ten of window w and the value before them in registers
+            double before = 0.0, mine[10];
+            const int n_win_round = n_round / 10;
+            for (int w = 0; w < n_win_round; w++) {
+                const double a_in = ar;
+                double t[10];
+#pragma unroll
+                for (int k = 0; k < 10; k++) {
+                    ar = ar_next(pacf, ar, z[w * 10 + k]);      // noise_gen.py:86-88
+                    t[k] = ar;
+                }
+                if (w == lane) {
+                    before = a_in;
+#pragma unroll
+                    for (int k = 0; k < 10; k++) mine[k] = t[k];
+                }
             }
-            __syncwarp();
             if (win < n_windows) {
                 double knots[11];
-                const double a0 = lane == 0 ? ar_in : av[lane * 10 - 1];
-                knots[0] = xi + lambda * sinh((a0 - gamma) / delta);            // the knot carried over, noise_gen.py:33-36
+                knots[0] = johnson(before, gamma, lambda, delta, xi);           // the knot carried over, noise_gen.py:33-36
 #pragma unroll
-                for (int k = 1; k <= 10; k++) knots[k] = xi + lambda * sinh((av[lane * 10 + k - 1] - gamma) / delta);
+                for (int k = 1; k <= 10; k++) knots[k] = johnson(mine[k - 1], gamma, lambda, delta, xi);
                 for (int r = 1; r < nsample; r++) {
                     const int64_t pos = win * per_window + r - 1;
                     if (pos >= n_noise) break;
-                    double v = 0.0;
-#pragma unroll
-                    for (int k = 0; k < 11; k++) v += sW[r * 11 + k] * knots[k];
-                    out[pos * n + e] = v;
+                    out[pos * n + e] = interp11(sW + r * 11, knots);
                 }
             }
             __syncwarp();
@@ -256,6 +276,43 @@ __global__ void __launch_bounds__(256) uniform_kernel(double *out, int64_t n, do
     out[i] = lo + (hi - lo) * rng.uniform();
 }
 
+// Book-keeping of a lockstep vector environment around its per-environment resets (envs/vector_env.py), one launch each
+// instead of a dozen elementwise ones.  vec_finish: after an env-step, which environments ended their episode (the
+// step reported done, env.py:103, or the episode reached the horizon) and the Philox key of the episode that replaces
+// each one.  vec_restart: after the masked reset, count the new episodes and merge the first observations in.
+__global__ void __launch_bounds__(256) vec_finish_kernel(const double *row, int64_t n, int done_row, int obs_row,
+                                                        int32_t *episode_steps, int32_t horizon,
+                                                        const int64_t *episodes_started, int64_t env0, int64_t group,
+                                                        int key_shift, int32_t *mask, int64_t *key, double *terminal_obs,
+                                                        uint8_t *done, uint8_t *truncated)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const int32_t steps = episode_steps[e] + 1;
+    episode_steps[e] = steps;
+    const bool d = row[(int64_t)done_row * n + e] != 0.0;
+    const bool fin = d || steps >= horizon;
+    mask[e] = fin ? 1 : 0;
+    key[e] = (((env0 + e) / group) << key_shift) | episodes_started[e];
+    terminal_obs[e] = row[(int64_t)obs_row * n + e];
+    done[e] = d ? 1 : 0;
+    truncated[e] = (fin && !d) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256) vec_restart_kernel(const int32_t *mask, int64_t n, int64_t *episodes_started,
+                                                         int32_t *episode_steps, const double *obs_new,
+                                                         const double *obs_step, double *obs_out)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const bool fin = mask[e] != 0;
+    if (fin) {
+        episodes_started[e] += 1;
+        episode_steps[e] = 0;
+    }
+    obs_out[e] = fin ? obs_new[e] : obs_step[e];
+}
+
 inline unsigned blocks(int64_t n, int b) { return (unsigned)((n + b - 1) / b); }
 
 }  // namespace
@@ -340,6 +397,29 @@ int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, 
 {
     if (!out || n <= 0) return SG_ERR_ARG;
     uniform_kernel<<<blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(out, n, lo, hi, seed, offset);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_vec_finish(const double *row, int64_t n_envs, int32_t done_row, int32_t obs_row, int32_t *episode_steps,
+                  int32_t horizon_steps, const int64_t *episodes_started, int64_t env_offset, int64_t group_size,
+                  int32_t key_shift, int32_t *mask, int64_t *key, double *terminal_obs, uint8_t *done, uint8_t *truncated,
+                  void *stream)
+{
+    if (!row || !episode_steps || !episodes_started || !mask || !key || !terminal_obs || !done || !truncated ||
+        n_envs <= 0 || group_size < 1 || key_shift < 1 || key_shift > 40 || done_row < 0 || obs_row < 0)
+        return SG_ERR_ARG;
+    vec_finish_kernel<<<blocks(n_envs, 256), 256, 0, (cudaStream_t)stream>>>(
+        row, n_envs, done_row, obs_row, episode_steps, horizon_steps, episodes_started, env_offset, group_size, key_shift,
+        mask, key, terminal_obs, done, truncated);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_vec_restart(const int32_t *mask, int64_t n_envs, int64_t *episodes_started, int32_t *episode_steps,
+                   const double *obs_new, const double *obs_step, double *obs_out, void *stream)
+{
+    if (!mask || !episodes_started || !episode_steps || !obs_new || !obs_step || !obs_out || n_envs <= 0) return SG_ERR_ARG;
+    vec_restart_kernel<<<blocks(n_envs, 256), 256, 0, (cudaStream_t)stream>>>(mask, n_envs, episodes_started,
+                                                                              episode_steps, obs_new, obs_step, obs_out);
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 

@@ -535,6 +535,12 @@ __global__ void __launch_bounds__(256) math_probe_kernel(int kind, const double 
     case 6: r = sgm::exp_core(u); break;
     case 7: r = exp(u); break;
     case 8: r = sgm::log_core(u); break;
+    case 9: r = log(u); break;
+    case 10: r = 2.0 * sgm::tanh_sum_half(2.0 * u, 2.0 * v); break;      // tanh(u) - tanh(v) + 2 as the RHS forms it
+    case 11: r = tanh(u) - tanh(v) + 2.0; break;
+    case 12: r = sgm::rcp_ulp(u); break;
+    case 13: r = (sgm::is_neg(u) ? 1.0 : 0.0) + (sgm::is_pos(u) ? 2.0 : 0.0); break;
+    case 14: r = sgm::exp_tanh(u); break;
     default: r = log(u); break;
     }
     out[i] = r;

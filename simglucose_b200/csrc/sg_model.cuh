@@ -99,7 +99,7 @@ __device__ __forceinline__ void stage_params(const ColT &c, Load p)
 {
     const double kmax = p(P_kmax), kmin = p(P_kmin), kabs = p(P_kabs);
     const double m1 = p(P_m1), m2 = p(P_m2), ka1 = p(P_ka1), kd = p(P_kd);
-    c.set(H_kmax, kmax); c.set(H_kmin, kmin); c.set(H_hk, (kmax - kmin) / 2.0);
+    c.set(H_kmax, kmax); c.set(H_kmin, kmin); c.set(H_hk, SG_TANH_SUM ? 2.0 * ((kmax - kmin) / 2.0) : (kmax - kmin) / 2.0);   // doubling is exact
     c.set(H_b, p(P_b)); c.set(H_d, p(P_d)); c.set(H_kabs, kabs); c.set(H_fk, p(P_f) * kabs);
     c.set(H_BW, p(P_BW)); c.set(H_kp1, p(P_kp1)); c.set(H_kp2, p(P_kp2)); c.set(H_kp3, p(P_kp3));
     c.set(H_Fsnc, p(P_Fsnc)); c.set(H_ke1, p(P_ke1)); c.set(H_ke2, p(P_ke2));
@@ -134,7 +134,7 @@ __device__ __forceinline__ Minute minute_setup_rate(const Column<BLOCK> &c, doub
     m.d = cho * 1000.0;
     m.ins = ins_per_kg;
     const double Dbar = last_Qsto + last_food * 1000.0;
-    m.fed = Dbar > 0.0;
+    m.fed = SG_INT_SIGN ? sgm::is_pos(Dbar) : Dbar > 0.0;
     // Dbar only moves while the patient eats: the four quotients / products below are recomputed when it did
     // (same inputs, same results -- the cache cannot change a bit)
     if (m.fed && Dbar != c(H_Dbar)) {                       // t1dpatient.py:136-140
@@ -157,7 +157,7 @@ __device__ __forceinline__ Minute minute_setup(const Column<BLOCK> &c, double ch
     m.d = cho * 1000.0;
     m.ins = insulin * 6000.0 / c(H_BW);
     const double Dbar = last_Qsto + last_food * 1000.0;
-    m.fed = Dbar > 0.0;
+    m.fed = SG_INT_SIGN ? sgm::is_pos(Dbar) : Dbar > 0.0;
     if (m.fed) {                                            // t1dpatient.py:136-140
         c.set(H_aa, 5.0 / 2.0 / (1.0 - c(H_b)) / Dbar);
         c.set(H_cc, 5.0 / 2.0 / c(H_d) / Dbar);
@@ -173,7 +173,11 @@ __device__ __forceinline__ double mask_nonneg(double x, double dx)
 {
     // (x >= 0) * dxdt, t1dpatient.py:167,173,179,191,195,198,202 (the sign of a zero result is
     // not preserved; it never reaches an output)
+#if SG_INT_SIGN
+    return sgm::is_neg(x) ? 0.0 : dx;
+#else
     return x >= 0.0 ? dx : 0.0;
+#endif
 }
 
 // T1DPatient.model, t1dpatient.py:118-208.  Parameters arrive two per shared-memory load (Column::pair).
@@ -188,9 +192,15 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     // :135-142, branch-free: tanh(aa*(qsto - b*Dbar)) - tanh(cc*(qsto - d*Dbar)) in one expression (sg_math.cuh),
     // evaluated for every lane and discarded by the select when Dbar == 0
     const double2 ab = m.ab, cd = m.cd;                                     // (2 aa, b*Dbar), (2 cc, d*Dbar)
+    const double2 kh = c.pair(H_kmin);                                      // kmin, (kmax - kmin) / 2 (SG_TANH_SUM: twice that)
+#if SG_TANH_SUM
+    // kmin + hk * (tanh(..) - tanh(..) + 2) with the bracket as one transcendental quantity T (sg_math.cuh tanh_sum_half
+    // returns T / 2; hk * T == (2 hk) * (T / 2) exactly, and the row H_hk holds 2 hk)
+    const double kfed = kh.x + kh.y * sgm::tanh_sum_half(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
+#else
     const double tdiff = sgm::tanh_diff2(ab.x * (qsto - ab.y), cd.x * (qsto - cd.y));
-    const double2 kh = c.pair(H_kmin);                                      // kmin, (kmax - kmin) / 2
     const double kfed = kh.x + kh.y * (tdiff + 2.0);
+#endif
     const double kgut = m.fed ? kfed : kmax;
     dx[1] = kmax * x[0] - x[1] * kgut;                                      // :145
     dx[2] = kgut * x[1] - kk.y * x[2];                                      // :148
@@ -199,8 +209,14 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     const double2 kp = c.pair(H_kp2);                                       // kp2, kp3
     const double EGPt = rk.y - kp.x * x[3] - kp.y * x[8];                   // :153
     const double2 ke = c.pair(H_ke2);                                       // ke2, ke1
+#if SG_INT_SIGN
+    const double over = x[3] - ke.x;                                        // x3 > ke2 <=> x3 - ke2 > 0 (exact in IEEE)
+    const double Et = sgm::is_pos(over) ? ke.y * over : 0.0;                // :158-161
+    const double egp = sgm::is_neg(EGPt) ? 0.0 : EGPt;                      // max(EGPt, 0) :165
+#else
     const double Et = (x[3] > ke.x) ? ke.y * (x[3] - ke.x) : 0.0;           // :158-161
     const double egp = (0.0 > EGPt) ? 0.0 : EGPt;                           // max(EGPt, 0) :165
+#endif
     const double2 k12 = c.pair(H_k1), fk = c.pair(H_Fsnc);                  // (k1, k2), (Fsnc, Km0)
     dx[3] = egp + Rat - fk.x - Et - k12.x * x[3] + k12.y * x[4];            // :165-166
     const double2 vm = c.pair(H_Vm0);                                       // Vm0, Vmx
@@ -392,6 +408,26 @@ __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
     for (int i = 0; i < NV; i += 2) {
         const double2 y2 = c.pair(H_Y + i), k2 = c.pair(H_K1 + i);
         double2 r2;
+#if SG_FAST_HINIT
+        // the quotients by the scale through a reciprocal refined to an ulp: HINIT is a heuristic guess of the first step
+        // size from two norms, a real-valued function like the error norm (sg_math.cuh rcp_ulp)
+        {
+            const double yi = y2.x;
+            const double r = sgm::rcp_ulp(ATOL + RTOL * fabs(yi));
+            const double a = k2.x * r, b = yi * r;
+            dnf = dnf + a * a;
+            dny = dny + b * b;
+            r2.x = r;
+        }
+        {
+            const double yi = y2.y;
+            const double r = sgm::rcp_ulp(ATOL + RTOL * fabs(yi));
+            const double a = k2.y * r, b = yi * r;
+            dnf = dnf + a * a;
+            dny = dny + b * b;
+            r2.y = r;
+        }
+#else
         {
             const double yi = y2.x;
             const double r = sgm::rcp_nr(ATOL + RTOL * fabs(yi));
@@ -410,6 +446,7 @@ __device__ __noinline__ HinitGuess hinit_first(double *col, double hmax)
             dny = dny + b * b;
             r2.y = r;
         }
+#endif
         c.set_pair(H_PE + i, r2);                            // the second half divides by the same scales
     }
     // dny / dnf through div_nr: bit-identical for these operands (both above 1e-10)
@@ -426,7 +463,21 @@ __device__ __noinline__ double hinit_second(double *col, double h, double dnf, d
     double der2 = 0.0;
 #pragma unroll 1
     for (int i = 0; i < NV; i += 2) {
+#if SG_FAST_HINIT
+        const double2 k2 = c.pair(H_K1 + i), f2 = c.pair(H_P7 + i), r2 = c.pair(H_PE + i);
+#else
         const double2 y2 = c.pair(H_Y + i), k2 = c.pair(H_K1 + i), f2 = c.pair(H_P7 + i), r2 = c.pair(H_PE + i);
+#endif
+#if SG_FAST_HINIT
+        {
+            const double a = (f2.x - k2.x) * r2.x;                // reciprocal left by the first half
+            der2 = der2 + a * a;
+        }
+        {
+            const double a = (f2.y - k2.y) * r2.y;
+            der2 = der2 + a * a;
+        }
+#else
         {
             const double sk = ATOL + RTOL * fabs(y2.x);
             const double a = sgm::div_r(f2.x - k2.x, sk, r2.x);   // reciprocal left by the first half
@@ -437,6 +488,7 @@ __device__ __noinline__ double hinit_second(double *col, double h, double dnf, d
             const double a = sgm::div_r(f2.y - k2.y, sk, r2.y);
             der2 = der2 + a * a;
         }
+#endif
     }
     der2 = sgm::div_nr(sqrt(der2), h);                       // h >= 1e-6
     const double der12 = fmax(fabs(der2), sqrt(dnf));

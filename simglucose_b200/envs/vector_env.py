@@ -113,6 +113,12 @@ class T1DSimVecEnv(object):
         self.episode_steps = torch.zeros(E, dtype=torch.int32, device=dev)        # env-steps of the current episode
         self.start_minutes = torch.full((E,), self.start_minute, dtype=torch.int32, device=dev)
         self._env_index = torch.arange(E, dtype=torch.int64, device=dev) + self.episode_offset
+        # outputs of the book-keeping kernels around per-environment resets (sg_vec_finish / sg_vec_restart)
+        self._mask = torch.zeros(E, dtype=torch.int32, device=dev)
+        self._key = torch.zeros(E, dtype=torch.int64, device=dev)
+        self._terminal_obs = torch.zeros(E, dtype=torch.float64, device=dev)
+        self._done = torch.zeros(E, dtype=torch.bool, device=dev)
+        self._truncated = torch.zeros(E, dtype=torch.bool, device=dev)
         if self.stream_mode == 'reference' and self.gym_seeding:
             # one gym np_random per environment (simglucose_gym_env.py:38); the wrapper's constructor already builds
             # one env from it (:39), which consumes the first chain of draws
@@ -131,9 +137,11 @@ class T1DSimVecEnv(object):
         hour = rng.randint(low=0.0, high=24.0)
         return int(seed2), int(seed3), int(seed4), int(hour)
 
-    def _new_episodes_device(self, mask):
-        """Philox streams for the environments in mask (int32 [E] device tensor, None = all), no host involvement."""
-        key = (self._env_index // self.group_size << _KEY_SHIFT) | self.episodes_started
+    def _new_episodes_device(self, mask, key=None):
+        """Philox streams for the environments in mask (int32 [E] device tensor, None = all), no host involvement.
+        key: the stream keys when the caller already has them (sg_vec_finish)."""
+        if key is None:
+            key = (self._env_index // self.group_size << _KEY_SHIFT) | self.episodes_started
         x0 = None
         if self.gym_seeding:
             S.device_episode_starts(key, self.patient_row, self._table_x0, n_draws=2, seed=self.seed, mask=mask,
@@ -254,10 +262,20 @@ class T1DSimVecEnv(object):
 
     def _after_step(self, row):
         self.steps += 1
-        self.episode_steps += 1
         self.info = self._info(row)
         reward = row[_T['reward']]
-        done = row[_T['done']] != 0
+        if self.auto_reset and self.stream_mode == 'device':
+            # one launch: episode_steps += 1, done, finished mask, truncation, terminal observation, keys of the new episodes
+            lib, E = self.engine.lib, self.num_envs
+            _capi.check(lib.sg_vec_finish(row.data_ptr(), E, _T['done'], _T['obs'], self.episode_steps.data_ptr(),
+                                          self.horizon_steps, self.episodes_started.data_ptr(), self.episode_offset,
+                                          self.group_size, _KEY_SHIFT, self._mask.data_ptr(), self._key.data_ptr(),
+                                          self._terminal_obs.data_ptr(), self._done.data_ptr(), self._truncated.data_ptr(),
+                                          torch.cuda.current_stream(self.device).cuda_stream))
+            done = self._done
+        else:
+            self.episode_steps += 1
+            done = row[_T['done']] != 0
         if self.cgm_window is not None:                                    # env.py:96, 100-102
             w = self.cgm_window
             w[:-1] = w[1:].clone()
@@ -271,17 +289,29 @@ class T1DSimVecEnv(object):
 
     def _reset_finished(self, row, done):
         """Per-environment reset of the episodes that reported done or reached the horizon."""
+        if self.stream_mode == 'device':
+            mask = self._mask                                              # filled by sg_vec_finish
+            self.info['terminal_obs'] = self._terminal_obs
+            self.info['truncated'] = self._truncated
+            x0 = self._new_episodes_device(mask, key=self._key)
+            self.engine.reset_masked(mask, x0=self._x0_for_reset(x0), row0=self._row0)
+            if self.cgm_window is not None:
+                finished = mask != 0
+                self.cgm_window[:, finished] = float('nan')
+                self.cgm_window[-1] = torch.where(finished, self._row0[_T['CGM']], self.cgm_window[-1])
+            _capi.check(self.engine.lib.sg_vec_restart(mask.data_ptr(), self.num_envs, self.episodes_started.data_ptr(),
+                                                       self.episode_steps.data_ptr(), self._row0[_T['obs']].data_ptr(),
+                                                       row[_T['obs']].data_ptr(), self._obs.data_ptr(),
+                                                       torch.cuda.current_stream(self.device).cuda_stream))
+            return self._obs
         finished = done | (self.episode_steps >= self.horizon_steps)
         mask = finished.to(torch.int32)
         self.info['terminal_obs'] = row[_T['obs']].clone()
         self.info['truncated'] = finished & ~done
-        if self.stream_mode == 'device':
-            x0 = self._new_episodes_device(mask)
-        else:
-            idx = finished.nonzero().reshape(-1).cpu().tolist()            # host streams: small populations
-            if not idx:
-                return row[_T['obs']]
-            x0 = self._new_episodes_reference(idx)
+        idx = finished.nonzero().reshape(-1).cpu().tolist()                # host streams: small populations
+        if not idx:
+            return row[_T['obs']]
+        x0 = self._new_episodes_reference(idx)
         self.engine.reset_masked(mask, x0=self._x0_for_reset(x0), row0=self._row0)
         self.episodes_started += mask.to(torch.int64)
         self.episode_steps.masked_fill_(finished, 0)

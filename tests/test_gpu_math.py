@@ -68,6 +68,44 @@ def test_tanh_diff_absolute_error():
     assert np.array_equal(_probe(2, big, -big), np.array([2.0, -2.0, 2.0, -2.0]))
 
 
+def test_tanh_sum_of_the_gastric_emptying_law():
+    """sg_math.cuh tanh_sum_half (what rhs() evaluates for t1dpatient.py:138-142): tanh(u) - tanh(v) + 2 as one quotient
+    of two positive polynomials in e^2u, e^2v, the exponentials through the nine-operation exp_tanh.  Relative error
+    <= 2 ulp of the O(1) value against CUDA's libm, also in saturation."""
+    rng = np.random.RandomState(12)
+    n = 1 << 21
+    u = np.concatenate([rng.uniform(-60.0, 5.0, n), rng.uniform(-3.0, 3.0, n), rng.uniform(-45.0, 45.0, n)])
+    v = np.concatenate([rng.uniform(-5.0, 30.0, n), rng.uniform(-3.0, 3.0, n), rng.uniform(-45.0, 45.0, n)])
+    got, ref = _probe(10, u, v), _probe(11, u, v)
+    assert np.max(np.abs(got - ref) / np.maximum(ref, 1.0)) <= 6.7e-16
+    assert np.max(np.abs(got - ref)) <= 2.0e-15
+    z = np.zeros(4)
+    assert np.array_equal(_probe(10, z, z), z + 2.0)
+    big = np.array([1e300, -1e300, 700.0, -700.0, np.inf, -np.inf])
+    sat = _probe(10, big, -big)                                     # saturation: 4 and 0 to the last place or two
+    assert np.all(np.abs(sat - np.array([4.0, 0.0, 4.0, 0.0, 4.0, 0.0])) <= 1.8e-15) and np.all(sat[1::2] >= 0.0)
+    assert np.all(np.abs(_probe(10, big, big) - 2.0) <= 9e-16)
+    # the exponential on its own: the one-part reduction costs |t| * 46 * 1.7e-18 relative, by design
+    t = rng.uniform(-80.0, 80.0, n)
+    got, ref = _probe(14, t, t), _probe(7, t, t)
+    assert np.max(np.abs(got - ref) / ref) <= 1.2e-14
+    small = np.abs(t) <= 5.0
+    assert np.max(np.abs(got[small] - ref[small]) / ref[small]) <= 1.0e-15
+
+
+def test_rcp_ulp_and_integer_sign_tests():
+    """rcp_ulp (error norm, HINIT norms): within 1.5 ulp of 1 / x for the scales the integrator divides by.  is_neg /
+    is_pos (the RHS's masks): exactly x < 0 and x > 0 for every non-NaN double, -0.0 and denormals included."""
+    rng = np.random.RandomState(13)
+    x = np.exp(rng.uniform(np.log(1e-13), np.log(1e6), 1 << 20))
+    got = _probe(12, x, x)
+    assert np.max(np.abs(got * x - 1.0)) <= 3.4e-16
+    tiny = np.array([5e-324, 2.2250738585072014e-308, 1e-300])
+    e = np.concatenate([[0.0, -0.0, np.inf, -np.inf, 1.0, -1.0], tiny, -tiny, rng.standard_normal(1000)])
+    got = _probe(13, e, e)
+    assert np.array_equal(got, (e < 0) * 1.0 + (e > 0) * 2.0)
+
+
 def test_pow_pos_step_controller_exponents():
     rng = np.random.RandomState(3)
     n = 1 << 20
