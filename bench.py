@@ -77,7 +77,8 @@ def parse():
     ap.add_argument('--fp32', action='store_true', help='optional FP32 mode (SG_FLAG_FP32): NOT the graded arithmetic')
     ap.add_argument('--coherence', type=int, default=-1,
                     help='env-steps between two sorts of the launch order (sg_set_coherence); -1 = the default of the '
-                         'workload (headline: 0, configs with independent schedules: 40)')
+                         'workload (40 for resident populations; 0 for the one-wave shards of the e2e leg, where every '
+                         'launch boundary costs a tail)')
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='target duration of the cpu_baseline sample')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
@@ -175,9 +176,10 @@ def kernel_sha16():
     return h.hexdigest()[:16]
 
 
-def measured_traffic(groups, days):
-    """DRAM bytes of one run_kernel launch from the committed ncu capture -- quoted only when the capture was taken on
-    the kernel sources of this tree (hash) and on this workload."""
+def measured_traffic(groups, days, coherence):
+    """DRAM bytes of the run_kernel launches of ONE pass (with a sorted launch order a pass is cut into launches of
+    `coherence` env-steps; their bytes are summed) from the committed ncu capture -- quoted only when the capture was
+    taken on the kernel sources of this tree (hash) and on this workload."""
     try:
         t = json.load(open(TRAFFIC_FILE))
     except Exception:
@@ -185,9 +187,11 @@ def measured_traffic(groups, days):
     if t.get('kernel_sha16') != kernel_sha16():
         return None, 'capture %s is of an older kernel (sha %s, tree %s): not quoted' % (
             t.get('source'), t.get('kernel_sha16'), kernel_sha16())
-    if t.get('groups') != groups or t.get('days') != days:
-        return None, 'capture is of another workload (%s groups x %s days)' % (t.get('groups'), t.get('days'))
-    return int(t['dram_bytes_per_launch']), 'ncu dram__bytes_read.sum + dram__bytes_write.sum, %s' % t.get('source')
+    if t.get('groups') != groups or t.get('days') != days or t.get('coherence_steps', 0) != coherence:
+        return None, 'capture is of another workload (%s groups x %s days, coherence %s)' % (
+            t.get('groups'), t.get('days'), t.get('coherence_steps', 0))
+    return int(t['dram_bytes_per_pass']), ('ncu dram__bytes_read.sum + dram__bytes_write.sum over the %d run_kernel '
+                                           'launches of one pass, %s' % (t.get('launches_per_pass', 1), t.get('source')))
 
 
 def cpu_sample(args, noise_h, mm_h, mg_h, rows_h, n_steps, threads, target_s):
@@ -579,7 +583,8 @@ def main():
     n_steps = args.days * 480
     n_min = n_steps * 3
     ep0 = rank * E                                    # weak scaling: every rank simulates its own E episodes
-    coherence = max(0, args.coherence)
+    coherence = 40 if args.coherence < 0 else args.coherence
+    coherence_e2e = 0 if args.coherence < 0 else args.coherence
     rows = (torch.arange(E, device=dev, dtype=torch.int64) % 30).to(torch.int32)
     rows_h = rows.cpu().numpy()
     ctrl_rows = controller_rows_device(rows)
@@ -646,22 +651,30 @@ def main():
         probe_ms = p0.elapsed_time(p1)
     peak_tf = 148 * 8 * 256 * iters * 16 / (probe_ms * 1e-3) / 1e12
     ach_tf = fl / (kern_ms * 1e-3) / 1e12
-    # algorithmic HBM bytes of one pass: state in/out, noise, meals, params, stats
-    hbm_bytes = E * (2 * (24 * 8 + 5 * 4) + 2 * 16 * 8 + (n_steps + 2) * 8 + mm.shape[0] * 12 + 32 * 8 + 4 * 8 + 4)
+    # algorithmic HBM bytes of one pass: noise, meals, statistics once; state in / out, controller rows, patient row and
+    # launch order once per launch (the parameter table itself is 8 KB and stays in L2)
+    n_launch_b = (n_steps + coherence - 1) // coherence if coherence > 0 else 1
+    hbm_bytes = E * ((n_steps + 2) * 8 + mm.shape[0] * 12 + 2 * 16 * 8 +
+                     n_launch_b * (2 * (24 * 8 + 5 * 4) + 4 * 8 + 4 + (4 if coherence > 0 else 0)))
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
     except Exception:
         pass
-    traffic, traffic_note = measured_traffic(args.groups, args.days)
+    traffic, traffic_note = measured_traffic(args.groups, args.days, coherence)
+    n_launch = (n_steps + coherence - 1) // coherence if coherence > 0 else 1
     roofline = {'bound': 'fp64', 'achieved': ach_tf, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': ach_tf / peak_tf,
-                'traffic': traffic, 'traffic_unit': 'bytes per launch' if traffic else None, 'traffic_source': traffic_note,
+                'traffic': traffic, 'traffic_unit': 'bytes per pass' if traffic else None, 'traffic_source': traffic_note,
                 'kernel': 'run_kernel', 'kernel_ms': kern_ms, 'kernel_sha16': kernel_sha16(),
+                'launches_per_pass': n_launch,
+                'per': 'pass = %d run_kernel launch(es) of %s env-steps over all episodes; achieved = algorithmic flops of '
+                       'the pass / summed launch time (CUDA events around eng.run, which also holds the %d sort launches)'
+                       % (n_launch, coherence if coherence > 0 else n_steps, 3 * n_launch if coherence > 0 else 0),
                 'peak_source': 'DFMA chain probe timed in this run (sg_probe_dfma); MEASURED_PEAKS.json has no FP64 entry',
                 'algorithmic_flops_per_launch': fl, 'dopri_steps_per_minute': float(a[14] / (E * n_min)),
                 'hbm': {'achieved_gbs': hbm_bytes / (kern_ms * 1e-3) / 1e9, 'peak_gbs': peaks.get('hbm_gbs', 6650.0),
                         'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',
-                        'algorithmic_bytes_per_launch': hbm_bytes}}
+                        'algorithmic_bytes_per_pass': hbm_bytes}}
 
     if args.fp32:                                     # the optional mode runs on the FP32 pipe: its own (nominal) ceiling
         sm_ghz = 1.965
@@ -689,7 +702,7 @@ def main():
         d2h = sum(t.numel() * 8 for t in stats_h) + n_sh * _capi.NSTAT * 8
         e2e_agg = [None]
         runner = ShardRunner(max(hi - lo for lo, hi in zip(cuts[:-1], cuts[1:])), device=local, slots=2,
-                             carry_h=args.carry_h, fma=args.fma, fp32=args.fp32, coherence=coherence)
+                             carry_h=args.carry_h, fma=args.fma, fp32=args.fp32, coherence=coherence_e2e)
 
         def e2e_pass():
             _, e2e_agg[0] = runner.run(shards, n_steps, controller='bb', stats_out=stats_h)
@@ -710,7 +723,7 @@ def main():
         e2e = {'value': world * E * n_min * n_e2e / (float(ms.item()) * 1e-3), 'unit': METRIC,
                'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h), 'steps': n_e2e,
                'wall_s': time.perf_counter() - t0, 'api': 'simglucose_b200.engine.ShardRunner.run',
-               'shards': n_sh, 'rows_check': float(e2e_agg[0][0])}
+               'shards': n_sh, 'coherence_steps': coherence_e2e, 'rows_check': float(e2e_agg[0][0])}
         runner.close()
         del shards, stats_h
 

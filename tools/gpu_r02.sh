@@ -14,14 +14,15 @@ fi
 timeout 300 python __graft_entry__.py smoke > $OUT/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $OUT/rc.txt
 timeout 1200 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?" | tee -a $OUT/rc.txt
 timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_reference.json 2> $OUT/bench_reference.err; echo "bench_ref rc=$?" | tee -a $OUT/rc.txt
-PROF="python bench.py --groups 1262 --days 1 --steps 1 --warmup 1 --no-cpu --no-e2e --no-configs"
+PROF="python bench.py --groups 1262 --days 1 --steps 1 --warmup 1 --no-cpu --no-e2e --no-configs --coherence 0"
 timeout 300 $PROF > $OUT/prof_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/launches.csv $PROF > $OUT/ncu_launches.log 2>&1
 echo "ncu launches rc=$?" | tee -a $OUT/rc.txt
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:run_kernel -c 1 -o $OUT/prof $PROF > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?" | tee -a $OUT/rc.txt
 # DRAM bytes of the run_kernel launch of the DEFAULT workload (8840 groups x 3 days), second launch (after one warm-up)
-timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:run_kernel -s 1 -c 1 --csv \
+# (default coherence 40: one pass = 36 launches of 40 env-steps; the first 36 are the warm-up pass)
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:run_kernel -s 36 -c 36 --csv \
   --log-file $OUT/run_kernel_dram_traffic.csv python bench.py --steps 1 --warmup 1 --no-cpu --no-e2e --no-configs > $OUT/ncu_traffic.log 2>&1
 echo "ncu traffic rc=$?" | tee -a $OUT/rc.txt
 if [[ " $* " != *" noconfigs "* ]]; then
