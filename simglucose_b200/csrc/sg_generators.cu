@@ -85,98 +85,93 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
 // The same streams for a FEW episodes of a large population (a vector environment restarting the episodes that ended
 // in this env-step: mask[e] != 0 for well under 1 % of them).  One thread per episode would leave 31 lanes of a warp idle
 // behind a lane that walks ~1000 normal deviates and writes ~480 samples 8 * n bytes apart.  Here a block of four warps
-// looks at its 128 episodes, lists the masked ones, and every warp takes listed episodes in turn; for one episode the 32
-// lanes own one 15-minute window each (32 windows per round):
-//   1. lane w draws the ten deviates of window w by random access into the Philox stream (Philox::block_at) -- the
-//      expensive part, 32 windows at a time;
-//   2. the AR chain ar <- pacf * (ar + z) is a serial recurrence: every lane walks the round's 320 deviates from shared
-//      memory (two dependent FP64 operations per deviate) and lane w keeps the values of window w;
-//   3. lane w transforms its eleven knots and interpolates the samples of its window.
+// looks at its 128 episodes, lists the masked ones, and works through the list one episode at a time with ALL its threads:
+// thread w owns the 15-minute window w (128 windows per round):
+//   1. thread w draws the ten deviates of window w by random access into the Philox stream (Philox::block_at) -- the
+//      expensive part (inverse normal CDF), 128 windows at a time;
+//   2. the AR chain ar <- pacf * (ar + z) is a serial recurrence: every thread walks the round's deviates from shared
+//      memory up to its own window (two dependent FP64 operations per deviate) and keeps the values of window w;
+//   3. thread w transforms its eleven knots and interpolates the samples of its window.
 // Same deviates, same chain, same expressions as noise_kernel: bit-identical streams (tests/test_gpu_generators.py).
-constexpr int NM_WARPS = 4;
+constexpr int NM_THREADS = 128;
 
-__global__ void __launch_bounds__(32 * NM_WARPS) noise_masked_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
-                                                                    const double *W, double pacf, double gamma,
-                                                                    double lambda, double delta, double xi, uint64_t seed,
-                                                                    const StreamSel sel)
+__global__ void __launch_bounds__(NM_THREADS) noise_masked_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
+                                                                 const double *W, double pacf, double gamma,
+                                                                 double lambda, double delta, double xi, uint64_t seed,
+                                                                 const StreamSel sel)
 {
     extern __shared__ double sW[];                         // nsample * 11 interpolation weights
-    __shared__ double zs[NM_WARPS][320];                   // deviates of a round
-    __shared__ int list[32 * NM_WARPS];
+    __shared__ double z[NM_THREADS * 10];                  // deviates of a round
+    __shared__ int list[NM_THREADS];
     __shared__ int n_list;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t mine = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (threadIdx.x == 0) n_list = 0;
+    __shared__ double ar_carry;                            // chain value at the end of a round
+    const int t = threadIdx.x, lane = t & 31;
+    const int64_t mine = (int64_t)blockIdx.x * blockDim.x + t;
+    if (t == 0) n_list = 0;
     __syncthreads();
     const bool sel_me = mine < n && !sel.skip(mine);
     const unsigned ballot = __ballot_sync(0xffffffffu, sel_me);
     int base_slot = 0;
     if (lane == 0 && ballot) base_slot = atomicAdd(&n_list, __popc(ballot));
     base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
-    if (sel_me) list[base_slot + __popc(ballot & ((1u << lane) - 1u))] = threadIdx.x;
+    if (sel_me) list[base_slot + __popc(ballot & ((1u << lane) - 1u))] = t;
     __syncthreads();
     const int count = n_list;
     if (count == 0) return;
-    for (int i = threadIdx.x; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
-    __syncthreads();
+    for (int i = t; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
     const int per_window = nsample - 1;
     const int64_t n_windows = (n_noise + per_window - 1) / per_window;
-    double *z = zs[warp];
-    for (int li = warp; li < count; li += NM_WARPS) {
+    for (int li = 0; li < count; li++) {                   // (the order inside the list cannot reach a result)
         const int64_t e = (int64_t)blockIdx.x * blockDim.x + list[li];
         const Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
         uint32_t w4[4];
         rng.block_at(0, w4);
-        double ar = Philox::normal_of(w4, 0);               // deviate 0: _noise_init, noise_gen.py:84-85
-        for (int64_t w0 = 0; w0 < n_windows; w0 += 32) {
-            const int64_t win = w0 + lane;
-            const int n_round = (int)min((int64_t)32, n_windows - w0) * 10;     // deviates of this round
+        double ar0 = Philox::normal_of(w4, 0);              // deviate 0: _noise_init, noise_gen.py:84-85
+        for (int64_t w0 = 0; w0 < n_windows; w0 += NM_THREADS) {
+            const int64_t win = w0 + t;
+            __syncthreads();                                // z and ar_carry of the round before are consumed
             if (win < n_windows) {
                 // deviates 1 + 10 win .. 10 + 10 win: an odd first index, i.e. the second half of one draw block, four
                 // whole blocks, the first half of a sixth
                 const uint32_t b0 = (uint32_t)((1 + 10 * win) >> 1);
                 rng.block_at(b0, w4);
-                z[lane * 10 + 0] = Philox::normal_of(w4, 1);
+                z[t * 10 + 0] = Philox::normal_of(w4, 1);
 #pragma unroll
                 for (int b = 1; b <= 4; b++) {
                     rng.block_at(b0 + b, w4);
-                    z[lane * 10 + 2 * b - 1] = Philox::normal_of(w4, 0);
-                    z[lane * 10 + 2 * b] = Philox::normal_of(w4, 1);
+                    z[t * 10 + 2 * b - 1] = Philox::normal_of(w4, 0);
+                    z[t * 10 + 2 * b] = Philox::normal_of(w4, 1);
                 }
                 rng.block_at(b0 + 5, w4);
-                z[lane * 10 + 9] = Philox::normal_of(w4, 0);
+                z[t * 10 + 9] = Philox::normal_of(w4, 0);
             }
-            __syncwarp();
-            // the chain, window by window: every lane computes every value (two dependent FP64 operations per deviate,
-            // the loads run ahead), lane w keeps the ten of window w and the value before them in registers
-            double before = 0.0, mine[10];
-            const int n_win_round = n_round / 10;
-            for (int w = 0; w < n_win_round; w++) {
-                const double a_in = ar;
-                double t[10];
+            __syncthreads();
+            // the chain up to this thread's window: the windows before it only advance ar, its own is kept
+            const int n_win_round = (int)min((int64_t)NM_THREADS, n_windows - w0);
+            const int last = t < n_win_round ? t : n_win_round - 1;
+            double ar = ar0, before = 0.0, mine_ar[10];
+            for (int w = 0; w <= last; w++) {
+                before = ar;
 #pragma unroll
                 for (int k = 0; k < 10; k++) {
                     ar = ar_next(pacf, ar, z[w * 10 + k]);      // noise_gen.py:86-88
-                    t[k] = ar;
-                }
-                if (w == lane) {
-                    before = a_in;
-#pragma unroll
-                    for (int k = 0; k < 10; k++) mine[k] = t[k];
+                    mine_ar[k] = ar;
                 }
             }
+            if (t == n_win_round - 1) ar_carry = ar;
             if (win < n_windows) {
                 double knots[11];
                 knots[0] = johnson(before, gamma, lambda, delta, xi);           // the knot carried over, noise_gen.py:33-36
 #pragma unroll
-                for (int k = 1; k <= 10; k++) knots[k] = johnson(mine[k - 1], gamma, lambda, delta, xi);
+                for (int k = 1; k <= 10; k++) knots[k] = johnson(mine_ar[k - 1], gamma, lambda, delta, xi);
                 for (int r = 1; r < nsample; r++) {
                     const int64_t pos = win * per_window + r - 1;
                     if (pos >= n_noise) break;
                     out[pos * n + e] = interp11(sW + r * 11, knots);
                 }
             }
-            __syncwarp();
+            __syncthreads();
+            ar0 = ar_carry;
         }
     }
 }
@@ -338,7 +333,7 @@ int sg_gen_noise_keyed(double *out, int64_t n_episodes, int64_t n_noise, int32_t
         return SG_ERR_ARG;
     const StreamSel sel{0, 1, key, mask};
     if (mask)       // a few columns of a resident buffer: warp-cooperative
-        noise_masked_kernel<<<blocks(n_episodes, 32 * NM_WARPS), 32 * NM_WARPS, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+        noise_masked_kernel<<<blocks(n_episodes, NM_THREADS), NM_THREADS, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
             out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
             model_host[4], seed, sel);
     else

@@ -649,15 +649,19 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             }
             phase = PH_S3;
             } else if (phase & PH_S3) {                                          // kt = k3
+            // Register hand-over: P4 is consumed by this stage, so its registers take the stage-7 sum from here on
+            // (P4 = A71 k1 + A73 k3 + ..); P5 is consumed by the next stage and takes the error sum there.  Only the
+            // error sum's first two terms travel through shared memory (H_PE), for one stage.  Same operations in the
+            // same order as with both sums in shared memory: bit-identical, 84 of 98 LDS / STS.128 per step fewer.
             SG_FOR_PAIRS(i) {
                 const double2 k2 = c.pair(H_K1 + i), y2 = yy[i / 2];
-                double2 p7 = make_double2(0.0, 0.0), pe = make_double2(0.0, 0.0);
+                double2 pe = make_double2(0.0, 0.0);
                 {
                     const double k1 = k2.x;
                     yt[i] = y2.x + h * (P4[i] + A43 * kt[i]);
                     P5[i] = P5[i] + A53 * kt[i];
                     P6[i] = P6[i] + A63 * kt[i];
-                    p7.x = A71 * k1 + A73 * kt[i];
+                    P4[i] = A71 * k1 + A73 * kt[i];
                     pe.x = E1 * k1 + E3 * kt[i];
                 }
                 if (i + 1 < NX) {
@@ -666,32 +670,28 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
                     yt[q] = y2.y + h * (P4[q] + A43 * kt[q]);
                     P5[q] = P5[q] + A53 * kt[q];
                     P6[q] = P6[q] + A63 * kt[q];
-                    p7.y = A71 * k1 + A73 * kt[q];
+                    P4[q] = A71 * k1 + A73 * kt[q];
                     pe.y = E1 * k1 + E3 * kt[q];
                 }
-                c.set_pair(H_P7 + i, p7);
                 c.set_pair(H_PE + i, pe);
             }
             phase = PH_S4;
             } else {                                          // kt = k4
             SG_FOR_PAIRS(i) {
-                const double2 y2 = yy[i / 2];
-                double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
+                const double2 y2 = yy[i / 2], pe = c.pair(H_PE + i);
                 {
                     yt[i] = y2.x + h * (P5[i] + A54 * kt[i]);
                     P6[i] = P6[i] + A64 * kt[i];
-                    p7.x = p7.x + A74 * kt[i];
-                    pe.x = pe.x + E4 * kt[i];
+                    P4[i] = P4[i] + A74 * kt[i];
+                    P5[i] = pe.x + E4 * kt[i];
                 }
                 if (i + 1 < NX) {
                     const int q = i + 1 < NX ? i + 1 : i;
                     yt[q] = y2.y + h * (P5[q] + A54 * kt[q]);
                     P6[q] = P6[q] + A64 * kt[q];
-                    p7.y = p7.y + A74 * kt[q];
-                    pe.y = pe.y + E4 * kt[q];
+                    P4[q] = P4[q] + A74 * kt[q];
+                    P5[q] = pe.y + E4 * kt[q];
                 }
-                c.set_pair(H_P7 + i, p7);
-                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S5;
             }
@@ -699,36 +699,31 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             if (phase & PH_S5) {                                          // kt = k5
             SG_FOR_PAIRS(i) {
                 const double2 y2 = yy[i / 2];
-                double2 p7 = c.pair(H_P7 + i), pe = c.pair(H_PE + i);
                 {
                     yt[i] = y2.x + h * (P6[i] + A65 * kt[i]);
-                    p7.x = p7.x + A75 * kt[i];
-                    pe.x = pe.x + E5 * kt[i];
+                    P4[i] = P4[i] + A75 * kt[i];
+                    P5[i] = P5[i] + E5 * kt[i];
                 }
                 if (i + 1 < NX) {
                     const int q = i + 1 < NX ? i + 1 : i;
                     yt[q] = y2.y + h * (P6[q] + A65 * kt[q]);
-                    p7.y = p7.y + A75 * kt[q];
-                    pe.y = pe.y + E5 * kt[q];
+                    P4[q] = P4[q] + A75 * kt[q];
+                    P5[q] = P5[q] + E5 * kt[q];
                 }
-                c.set_pair(H_P7 + i, p7);
-                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S6;
             } else if (phase & PH_S6) {                                          // kt = k6; yt becomes the 5th-order solution
             SG_FOR_PAIRS(i) {
-                const double2 y2 = yy[i / 2], p7 = c.pair(H_P7 + i);
-                double2 pe = c.pair(H_PE + i);
+                const double2 y2 = yy[i / 2];
                 {
-                    yt[i] = y2.x + h * (p7.x + A76 * kt[i]);
-                    pe.x = pe.x + E6 * kt[i];
+                    yt[i] = y2.x + h * (P4[i] + A76 * kt[i]);
+                    P5[i] = P5[i] + E6 * kt[i];
                 }
                 if (i + 1 < NX) {
                     const int q = i + 1 < NX ? i + 1 : i;
-                    yt[q] = y2.y + h * (p7.y + A76 * kt[q]);
-                    pe.y = pe.y + E6 * kt[q];
+                    yt[q] = y2.y + h * (P4[q] + A76 * kt[q]);
+                    P5[q] = P5[q] + E6 * kt[q];
                 }
-                c.set_pair(H_PE + i, pe);
             }
             phase = PH_S7;
             } else {                                           // kt = k7 = f(x + h, y1): error estimate + control
@@ -754,30 +749,23 @@ __device__ __forceinline__ int dopri5_minute(const Column<BLOCK> &c, const Minut
             for (int i = 0; i < NX; i++) ee[i] = fma(ee[i], ee[i], ee[i]);
 #pragma unroll
             for (int i = 0; i < NX; i++) rr[i] = fma(rr[i], ee[i], rr[i]);
-            SG_FOR_PAIRS(i) {
-                const double2 pe = c.pair(H_PE + i);
-                {
-                    const double a = ((pe.x + E7 * kt[i]) * h) * rr[i];
-                    err = err + a * a;
-                }
-                if (i + 1 < NX) {
-                    const int q = i + 1 < NX ? i + 1 : i;
-                    const double a = ((pe.y + E7 * kt[q]) * h) * rr[q];
-                    err = err + a * a;
-                }
+#pragma unroll
+            for (int i = 0; i < NX; i++) {
+                const double a = ((P5[i] + E7 * kt[i]) * h) * rr[i];
+                err = err + a * a;
             }
 #else
             SG_FOR_PAIRS(i) {
-                const double2 y2 = yy[i / 2], pe = c.pair(H_PE + i);
+                const double2 y2 = yy[i / 2];
                 {
-                    const double e = (pe.x + E7 * kt[i]) * h;
+                    const double e = (P5[i] + E7 * kt[i]) * h;
                     const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.x), fabs(yt[i]));
                     const double a = SG_ERR_QUOT(e, sk);
                     err = err + a * a;
                 }
                 if (i + 1 < NX) {
                     const int q = i + 1 < NX ? i + 1 : i;
-                    const double e = (pe.y + E7 * kt[q]) * h;
+                    const double e = (P5[q] + E7 * kt[q]) * h;
                     const double sk = ATOL + RTOL * sgm::max_sel(fabs(y2.y), fabs(yt[q]));
                     const double a = SG_ERR_QUOT(e, sk);
                     err = err + a * a;
