@@ -89,8 +89,8 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
 // thread w owns the 15-minute window w (128 windows per round):
 //   1. thread w draws the ten deviates of window w by random access into the Philox stream (Philox::block_at) -- the
 //      expensive part (inverse normal CDF), 128 windows at a time;
-//   2. the AR chain ar <- pacf * (ar + z) is a serial recurrence: every thread walks the round's deviates from shared
-//      memory up to its own window (two dependent FP64 operations per deviate) and keeps the values of window w;
+//   2. the AR chain ar <- pacf * (ar + z) is a serial recurrence: one thread walks the round's deviates in shared memory
+//      (two dependent FP64 operations per deviate) and overwrites each with the chain value;
 //   3. thread w transforms its eleven knots and interpolates the samples of its window.
 // Same deviates, same chain, same expressions as noise_kernel: bit-identical streams (tests/test_gpu_generators.py).
 constexpr int NM_THREADS = 128;
@@ -146,24 +146,25 @@ __global__ void __launch_bounds__(NM_THREADS) noise_masked_kernel(double *out, i
                 z[t * 10 + 9] = Philox::normal_of(w4, 0);
             }
             __syncthreads();
-            // the chain up to this thread's window: the windows before it only advance ar, its own is kept
+            // the chain: ONE thread walks the round's deviates and leaves the chain value in each deviate's slot (all
+            // 128 threads doing it redundantly would saturate the FP64 pipe of an SM that holds sixteen such blocks)
             const int n_win_round = (int)min((int64_t)NM_THREADS, n_windows - w0);
-            const int last = t < n_win_round ? t : n_win_round - 1;
-            double ar = ar0, before = 0.0, mine_ar[10];
-            for (int w = 0; w <= last; w++) {
-                before = ar;
-#pragma unroll
-                for (int k = 0; k < 10; k++) {
-                    ar = ar_next(pacf, ar, z[w * 10 + k]);      // noise_gen.py:86-88
-                    mine_ar[k] = ar;
+            if (t == 0) {
+                double ar = ar0;
+#pragma unroll 10
+                for (int j = 0; j < n_win_round * 10; j++) {
+                    ar = ar_next(pacf, ar, z[j]);               // noise_gen.py:86-88
+                    z[j] = ar;
                 }
+                ar_carry = ar;
             }
-            if (t == n_win_round - 1) ar_carry = ar;
+            __syncthreads();
+            const double before = t == 0 ? ar0 : z[t * 10 - 1];
             if (win < n_windows) {
                 double knots[11];
                 knots[0] = johnson(before, gamma, lambda, delta, xi);           // the knot carried over, noise_gen.py:33-36
 #pragma unroll
-                for (int k = 1; k <= 10; k++) knots[k] = johnson(mine_ar[k - 1], gamma, lambda, delta, xi);
+                for (int k = 1; k <= 10; k++) knots[k] = johnson(z[t * 10 + k - 1], gamma, lambda, delta, xi);
                 for (int r = 1; r < nsample; r++) {
                     const int64_t pos = win * per_window + r - 1;
                     if (pos >= n_noise) break;
