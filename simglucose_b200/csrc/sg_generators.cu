@@ -10,6 +10,7 @@
 // any shard of a population can be generated independently on any GPU.
 #include "../../include/simglucose_b200.h"
 
+#include <climits>
 #include <cmath>
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -197,10 +198,11 @@ __global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, dou
             const double u = rng.uniform(), ut = rng.uniform(), za = rng.normal();
             if (!(u < prob[i])) continue;
             const double Fa = normcdf((lb[i] - mu[i]) / sd[i]), Fb = normcdf((ub[i] - mu[i]) / sd[i]);
-            double t = mu[i] + sd[i] * normcdfinv(Fa + ut * (Fb - Fa));
+            // (explicit fma: the masked kernel below must round these three expressions the same way)
+            double t = fma(sd[i], normcdfinv(fma(ut, Fb - Fa, Fa)), mu[i]);
             t = fmin(fmax(t, lb[i]), ub[i]);
             const int tmin = (int)rint(t);                               // np.round
-            const double grams = fmax(rint(amu[i] + asd[i] * za), 0.0);  // max(round(normal), 0)
+            const double grams = fmax(rint(fma(asd[i], za, amu[i])), 0.0);  // max(round(normal), 0)
             const int m = day * 1440 + tmin - start_minute;              // episode minute
             if (m < 0 || m >= horizon || m <= last) continue;            // duplicates: first wins (list.index)
             if (grams == 0.0) { last = m; continue; }                    // Action(meal=0) is "no meal" (get_action)
@@ -214,6 +216,96 @@ __global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, dou
     for (; pos < max_meals; pos++) {
         meal_minute[(int64_t)pos * n + e] = -1;
         meal_grams[(int64_t)pos * n + e] = 0.0;
+    }
+}
+
+// The same schedules for a FEW episodes of a large population (mask[e] != 0 for well under 1 %: the episodes a vector
+// environment restarts in this env-step).  With one thread per episode a warp would wait for its one masked lane to walk
+// up to 18 candidate meals (three inverse normal CDFs each); here the lanes of a warp take one candidate each -- candidate
+// c = 6 * day + slot consumes the words 6 c .. 6 c + 5 of the Philox stream, so any lane can draw it (Philox::block_at) --
+// and lane 0 then applies the sequential rules (in range, one meal per minute, first wins) in the order of the list.
+// Bit-identical to scenario_kernel (tests/test_gpu_generators.py).
+__global__ void __launch_bounds__(128) scenario_masked_kernel(int32_t *meal_minute, double *meal_grams, int64_t n,
+                                                             int max_meals, const int32_t *start_minute_rows,
+                                                             int horizon, uint64_t seed, const StreamSel sel)
+{
+    __shared__ int list[128];
+    __shared__ int n_list;
+    __shared__ int cand_m[4][32];                          // episode minute of the candidate, INT_MIN = not drawn
+    __shared__ double cand_g[4][32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int64_t mine = (int64_t)blockIdx.x * blockDim.x + t;
+    if (t == 0) n_list = 0;
+    __syncthreads();
+    const bool sel_me = mine < n && !sel.skip(mine);
+    const unsigned ballot = __ballot_sync(0xffffffffu, sel_me);
+    int base_slot = 0;
+    if (lane == 0 && ballot) base_slot = atomicAdd(&n_list, __popc(ballot));
+    base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
+    if (sel_me) list[base_slot + __popc(ballot & ((1u << lane) - 1u))] = t;
+    __syncthreads();
+    const int count = n_list;
+    const double prob[6] = {0.95, 0.3, 0.95, 0.3, 0.95, 0.3};
+    const double lb[6] = {300, 540, 600, 840, 960, 1200}, ub[6] = {540, 600, 840, 960, 1200, 1380};
+    const double mu[6] = {420, 570, 720, 900, 1080, 1290}, sd[6] = {60, 30, 60, 30, 60, 30};
+    const double amu[6] = {45, 10, 70, 10, 80, 10}, asd[6] = {10, 5, 10, 5, 10, 5};
+    for (int li = warp; li < count; li += 4) {
+        const int64_t e = (int64_t)blockIdx.x * blockDim.x + list[li];
+        const int start_minute = start_minute_rows[e];
+        const Philox rng(seed, sel.stream(e), 0x6d65616cu /* 'meal' */);
+        const int n_cand = 6 * ((start_minute + horizon + 1439) / 1440);
+        int pos = 0, last = -1;
+        for (int c0 = 0; c0 < n_cand; c0 += 32) {
+            const int c = c0 + lane;
+            int m = INT_MIN;
+            double grams = 0.0;
+            if (c < n_cand) {
+                const int day = c / 6, i = c - 6 * day;
+                // words 6 c .. 6 c + 5 of the stream, handed out from the top of each draw block: (3, 2), (1, 0)
+                uint32_t w0[4], w1[4];
+                const uint32_t b = (uint32_t)((6 * c) >> 2);
+                rng.block_at(b, w0);
+                rng.block_at(b + 1, w1);
+                double u, ut, za;
+                if ((c & 1) == 0) {
+                    u = Philox::uniform_of(w0[3], w0[2]); ut = Philox::uniform_of(w0[1], w0[0]);
+                    za = normcdfinv(Philox::uniform_of(w1[3], w1[2]));
+                } else {
+                    u = Philox::uniform_of(w0[1], w0[0]); ut = Philox::uniform_of(w1[3], w1[2]);
+                    za = normcdfinv(Philox::uniform_of(w1[1], w1[0]));
+                }
+                if (u < prob[i]) {
+                    const double Fa = normcdf((lb[i] - mu[i]) / sd[i]), Fb = normcdf((ub[i] - mu[i]) / sd[i]);
+                    double tt = fma(sd[i], normcdfinv(fma(ut, Fb - Fa, Fa)), mu[i]);
+                    tt = fmin(fmax(tt, lb[i]), ub[i]);
+                    grams = fmax(rint(fma(asd[i], za, amu[i])), 0.0);
+                    m = day * 1440 + (int)rint(tt) - start_minute;
+                }
+            }
+            cand_m[warp][lane] = m;
+            cand_g[warp][lane] = grams;
+            __syncwarp();
+            if (lane == 0) {
+                const int n_here = min(32, n_cand - c0);
+                for (int k = 0; k < n_here; k++) {
+                    const int mk = cand_m[warp][k];
+                    if (mk == INT_MIN || mk < 0 || mk >= horizon || mk <= last) continue;   // duplicates: first wins
+                    const double g = cand_g[warp][k];
+                    if (g == 0.0) { last = mk; continue; }                                  // Action(meal=0) is "no meal"
+                    if (pos < max_meals) {
+                        meal_minute[(int64_t)pos * n + e] = mk;
+                        meal_grams[(int64_t)pos * n + e] = g;
+                        pos++; last = mk;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        if (lane == 0)
+            for (; pos < max_meals; pos++) {
+                meal_minute[(int64_t)pos * n + e] = -1;
+                meal_grams[(int64_t)pos * n + e] = 0.0;
+            }
     }
 }
 
@@ -363,8 +455,12 @@ int sg_gen_scenarios_keyed(int32_t *meal_minute, double *meal_grams, int64_t n_e
 {
     if (!meal_minute || !meal_grams || !start_minute || !key || n_episodes <= 0 || max_meals <= 0 || horizon_minutes <= 0)
         return SG_ERR_ARG;
-    scenario_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
-        meal_minute, meal_grams, n_episodes, max_meals, 0, start_minute, horizon_minutes, seed, StreamSel{0, 1, key, mask});
+    if (mask)       // a few columns of resident tables: warp-cooperative
+        scenario_masked_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
+            meal_minute, meal_grams, n_episodes, max_meals, start_minute, horizon_minutes, seed, StreamSel{0, 1, key, mask});
+    else
+        scenario_kernel<<<blocks(n_episodes, 128), 128, 0, (cudaStream_t)stream>>>(
+            meal_minute, meal_grams, n_episodes, max_meals, 0, start_minute, horizon_minutes, seed, StreamSel{0, 1, key, mask});
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 

@@ -142,6 +142,27 @@ def test_device_scenarios_match_random_scenario_distribution():
     mm6, _ = S.device_scenarios(4096, 1440, start_minute=600, seed=5, group_size=1)
     m6 = mm6.cpu().numpy()
     assert m6[m6 >= 0].min() >= 0 and ((m6[m6 >= 0] + 600) % 1440 >= 0).all() and m6.max() < 1440
+    # keyed schedules: the warp-cooperative kernel that rewrites a few masked columns of resident tables (one candidate
+    # meal per lane, random access into the Philox stream) gives the same tables as the one-thread-per-episode kernel,
+    # for every start hour and horizons of one to four calendar days (up to 24 candidates), and leaves the rest alone
+    import torch
+    n = 3000
+    key = torch.arange(n, device='cuda', dtype=torch.int64) * 5 + 3
+    for horizon in (480, 1440, 3 * 1440 + 77):
+        starts = ((torch.arange(n, device='cuda') * 37) % 1440).to(torch.int32)
+        M = 6 * ((1439 + horizon + 1439) // 1440)
+        full = S.device_scenarios_keyed(torch.full((M, n), -7, dtype=torch.int32, device='cuda'),
+                                        torch.full((M, n), -7.0, dtype=torch.float64, device='cuda'), starts, horizon, key, seed=21)
+        mask = (torch.arange(n, device='cuda') % 11 == 4).to(torch.int32)
+        part = S.device_scenarios_keyed(torch.full((M, n), -7, dtype=torch.int32, device='cuda'),
+                                        torch.full((M, n), -7.0, dtype=torch.float64, device='cuda'), starts, horizon, key, seed=21, mask=mask)
+        mb = mask.bool()
+        assert torch.equal(part[0][:, mb], full[0][:, mb]) and torch.equal(part[1][:, mb], full[1][:, mb])
+        assert bool((part[0][:, ~mb] == -7).all()) and bool((part[1][:, ~mb] == -7.0).all())
+        ones = torch.ones(n, dtype=torch.int32, device='cuda')
+        allm = S.device_scenarios_keyed(torch.zeros_like(full[0]), torch.zeros_like(full[1]), starts, horizon, key, seed=21, mask=ones)
+        assert torch.equal(allm[0], full[0]) and torch.equal(allm[1], full[1])
+        assert int((full[0] >= 0).sum()) > n * (horizon // 480)                                # the tables are not empty
     # the host table builder and the device kernel agree on how a schedule becomes a table (start 00:00, 1 day)
     hm, hg = S.random_scenario_table(3, 0, 1440)
     assert np.all(np.diff(hm) > 0) and np.all(hg > 0)
