@@ -317,15 +317,30 @@ class ShardRunner:
         self.capacity = int(capacity)
         self.engines = [BatchEngine(self.capacity, device=device, **engine_kw) for _ in range(max(1, int(slots)))]
         self.streams = [torch.cuda.Stream(device=self.device) for _ in self.engines]
+        self._trace_dev = self._trace_sel = None
 
-    def run(self, shards, n_steps, controller='bb', ctrl=None, stats_out=None):
+    def run(self, shards, n_steps, controller='bb', ctrl=None, stats_out=None, traces_out=None,
+            trace_cols=('BG', 'CGM', 'CHO', 'insulin')):
         """shards: iterable of dicts with host tensors / arrays, structure-of-arrays [rows, E_k] (pinned memory makes
           the copies asynchronous): patient_row [E_k], noise [n_steps + 2, E_k], meal_minute / meal_grams [M, E_k]
           and optionally ctrl_rows [4, E_k], x0 [13, E_k], params [32, E_k].
         stats_out: optional list of pinned [NSTAT, E_k] tensors that receive the per-episode statistics.
+        traces_out: optional list of pinned [n_steps, len(trace_cols), E_k] tensors that receive the trajectories (the
+          columns of the reference's result DataFrame, sim_engine.py:44-49 / env.py:169-180, one row per env-step; the
+          reset row is what reset(row0=...) returns); the device -> host copy of shard k overlaps the kernel of k + 1.
         Returns (stats_out, aggregate) -- aggregate is the population statistics vector [NSTAT] (numpy): sums, BG
-        extrema (rows 2, 3), episodes that reported done (row 13)."""
+        extrema (rows 2, 3), episodes that reported done (row 13).
+        (Measured and dropped: uploading the FIRST shard's noise in slices of env-steps on a copy stream, its run cut
+        likewise, so that the kernel starts after a third of the upload -- 4.6 % slower end to end than this plain
+        two-stream pipeline, profiles/r02_i_*.)"""
         shards = list(shards)
+        cols = [_capi.TRACE_COLS.index(c) for c in trace_cols]
+        if traces_out is not None and self._trace_dev is None:
+            self._trace_dev = [torch.empty(n_steps, _capi.NTRACE, self.capacity, dtype=torch.float64, device=self.device)
+                               for _ in self.engines]
+            self._trace_sel = [torch.empty(n_steps, len(cols), self.capacity, dtype=torch.float64, device=self.device)
+                               for _ in self.engines]
+            self._cols = torch.tensor(cols, dtype=torch.int64, device=self.device)
         if stats_out is None:
             stats_out = [torch.empty(_capi.NSTAT, int(torch.as_tensor(s['patient_row']).numel()),
                                      dtype=torch.float64).pin_memory() for s in shards]
@@ -339,7 +354,15 @@ class ShardRunner:
             with torch.cuda.stream(st):
                 eng.reset(sh['patient_row'], sh['noise'], sh.get('meal_minute'), sh.get('meal_grams'),
                           x0=sh.get('x0'), params=sh.get('params'), row0=False)
-                eng.run(n_steps, controller=controller, ctrl=ctrl, ctrl_rows=sh.get('ctrl_rows'), trace=False)
+                if traces_out is None:
+                    eng.run(n_steps, controller=controller, ctrl=ctrl, ctrl_rows=sh.get('ctrl_rows'), trace=False)
+                else:
+                    ek = eng.n
+                    tr = self._trace_dev[k % n].view(-1)[:n_steps * _capi.NTRACE * ek].view(n_steps, _capi.NTRACE, ek)
+                    eng.run(n_steps, controller=controller, ctrl=ctrl, ctrl_rows=sh.get('ctrl_rows'), trace=tr)
+                    sel = self._trace_sel[k % n].view(-1)[:n_steps * len(cols) * ek].view(n_steps, len(cols), ek)
+                    torch.index_select(tr, 1, self._cols, out=sel)
+                    traces_out[k].copy_(sel, non_blocking=True)
                 stats_out[k].copy_(eng.stats(), non_blocking=True)
                 aggs[k].copy_(eng.reduce_stats(), non_blocking=True)
         for st in self.streams:
@@ -354,6 +377,7 @@ class ShardRunner:
         for eng in self.engines:
             eng.close()
         self.engines = []
+        self._trace_dev = self._trace_sel = None
 
 
 def run_shards(shards, n_steps, controller='bb', ctrl=None, device=0, slots=2, stats_out=None, **engine_kw):

@@ -209,6 +209,22 @@ def test_run_shards_streams_host_population_identically():
         assert agg[k] == agg_want[k]
     for k in (1, 4, 5, 6, 7):
         assert abs(agg[k] - agg_want[k]) <= 1e-9 * max(1.0, abs(agg_want[k]))
+    # trajectories out: the selected history columns of every shard equal the resident batch's trace
+    from simglucose_b200 import _capi
+    from simglucose_b200.engine import ShardRunner
+    eng = BatchEngine(E)
+    eng.reset(rows, noise, mm, mg, row0=False)
+    trace = eng.run(n_steps, controller='bb', ctrl_rows=cr, trace=True)['trace']
+    cols = ('BG', 'CGM', 'CHO', 'insulin')
+    want_tr = trace[:, [_capi.TRACE_COLS.index(c) for c in cols], :].cpu()
+    eng.close()
+    runner = ShardRunner(max(hi - lo for lo, hi in zip(cuts[:-1], cuts[1:])), slots=2)
+    tr_out = [torch.empty(n_steps, len(cols), hi - lo, dtype=torch.float64).pin_memory() for lo, hi in zip(cuts[:-1], cuts[1:])]
+    stats2, agg2 = runner.run(shards, n_steps, controller='bb', traces_out=tr_out, trace_cols=cols)
+    torch.cuda.synchronize()
+    runner.close()
+    assert torch.equal(torch.cat(tr_out, dim=2), want_tr)
+    assert torch.equal(torch.cat(stats2, dim=1), want)
 
 
 def test_config3_shard_halves_reduce_to_the_single_engine_aggregate():
