@@ -303,6 +303,16 @@ int sg_gen_episode_starts(int32_t *start_minute, double *x0, const double *table
                           int64_t n_episodes, int32_t n_draws, uint64_t seed, const int64_t *key, const int32_t *mask,
                           void *stream);
 
+/* The keyed generators for a LIST of episodes (list [0 .. *count) on the device, as sg_vec_finish leaves it) instead of a
+ * mask: the thread blocks stride over the list, so the launch takes (listed / resident blocks) episodes of time however the
+ * listed episodes are spread over the population.  Same streams as the keyed (and masked) variants, bit for bit. */
+int sg_gen_noise_listed(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsample, const double *W_dev,
+                        const double *model_host, uint64_t seed, const int64_t *key, const int32_t *list,
+                        const int32_t *count, void *stream);
+int sg_gen_scenarios_listed(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
+                            const int32_t *start_minute, int32_t horizon_minutes, uint64_t seed, const int64_t *key,
+                            const int32_t *list, const int32_t *count, void *stream);
+
 /* Perturbed population (BASELINE.json configs[3]): params_soa[i][e] = table[row[e]][i] * (1 + amplitude*u),
  * u ~ U(-1, 1) i.i.d. per parameter.  table_dev: [n_rows][SG_NPARAM] on the device. */
 int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const int32_t *patient_row,
@@ -314,13 +324,15 @@ int sg_gen_perturbed_params(double *params_soa, const double *table_dev, const i
  * sg_vec_finish, after an env-step: episode_steps[e] += 1; done[e] = row[done_row][e] != 0 (env.py:103); mask[e] = done or
  *   episode_steps[e] >= horizon_steps; truncated[e] = mask and not done; terminal_obs[e] = row[obs_row][e];
  *   key[e] = ((env_offset + e) / group_size << key_shift) | episodes_started[e], the Philox stream of the episode that
- *   would replace e (sg_gen_*_keyed).  row: the [SG_NTRACE][n_envs] history row of the step.
+ *   would replace e (sg_gen_*_keyed).  row: the [SG_NTRACE][n_envs] history row of the step.  list / count (both or
+ *   neither): the environments with mask != 0 gathered into list[0 .. *count) in no particular order (device memory,
+ *   list [n_envs] int32, count [1] int32), for sg_gen_noise_listed / sg_gen_scenarios_listed.
  * sg_vec_restart, after sg_reset_masked(mask): episodes_started[e] += 1 and episode_steps[e] = 0 where mask[e] != 0;
  *   obs_out[e] = mask[e] ? obs_new[e] : obs_step[e]. */
 int sg_vec_finish(const double *row, int64_t n_envs, int32_t done_row, int32_t obs_row, int32_t *episode_steps,
                   int32_t horizon_steps, const int64_t *episodes_started, int64_t env_offset, int64_t group_size,
                   int32_t key_shift, int32_t *mask, int64_t *key, double *terminal_obs, uint8_t *done, uint8_t *truncated,
-                  void *stream);
+                  int32_t *list, int32_t *count, void *stream);
 int sg_vec_restart(const int32_t *mask, int64_t n_envs, int64_t *episodes_started, int32_t *episode_steps,
                    const double *obs_new, const double *obs_step, double *obs_out, void *stream);
 

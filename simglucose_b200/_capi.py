@@ -37,7 +37,8 @@ SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_har
            'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
            'sg_report_stats', 'sg_cvga_zones',
            'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma',
-           'sg_gen_noise_keyed', 'sg_gen_scenarios_keyed', 'sg_gen_episode_starts', 'sg_vec_finish', 'sg_vec_restart']
+           'sg_gen_noise_keyed', 'sg_gen_scenarios_keyed', 'sg_gen_episode_starts', 'sg_vec_finish', 'sg_vec_restart',
+           'sg_gen_noise_listed', 'sg_gen_scenarios_listed']
 
 
 class Hardware(C.Structure):
@@ -107,7 +108,9 @@ def load():
         L.sg_gen_scenarios_keyed.argtypes = [ip, dp, C.c_int64, C.c_int32, ip, C.c_int32, C.c_uint64, ip, ip, vp]
         L.sg_gen_episode_starts.argtypes = [ip, dp, dp, ip, C.c_int64, C.c_int32, C.c_uint64, ip, ip, vp]
         L.sg_vec_finish.argtypes = [dp, C.c_int64, C.c_int32, C.c_int32, ip, C.c_int32, ip, C.c_int64, C.c_int64, C.c_int32,
-                                    ip, ip, dp, ip, ip, vp]
+                                    ip, ip, dp, ip, ip, ip, ip, vp]
+        L.sg_gen_noise_listed.argtypes = [dp, C.c_int64, C.c_int64, C.c_int32, dp, C.POINTER(C.c_double), C.c_uint64, ip, ip, ip, vp]
+        L.sg_gen_scenarios_listed.argtypes = [ip, dp, C.c_int64, C.c_int32, ip, C.c_int32, C.c_uint64, ip, ip, ip, vp]
         L.sg_vec_restart.argtypes = [ip, C.c_int64, ip, ip, dp, dp, dp, vp]
     for name in SYMBOLS:
         f = getattr(L, name, None)

@@ -10,6 +10,7 @@
 // any shard of a population can be generated independently on any GPU.
 #include "../../include/simglucose_b200.h"
 
+#include <algorithm>
 #include <climits>
 #include <cmath>
 #include <cstdint>
@@ -96,6 +97,81 @@ __global__ void __launch_bounds__(128) noise_kernel(double *out, int64_t n, int6
 // Same deviates, same chain, same expressions as noise_kernel: bit-identical streams (tests/test_gpu_generators.py).
 constexpr int NM_THREADS = 128;
 
+// One episode's stream by the whole block (see above): z [NM_THREADS * 10] and ar_carry live in shared memory.
+__device__ __forceinline__ void noise_episode_by_block(double *out, int64_t n, int64_t n_noise, int nsample, const double *sW,
+                                                       double pacf, double gamma, double lambda, double delta, double xi,
+                                                       uint64_t seed, uint64_t stream, int64_t e, double *z, double *ar_carry)
+{
+    const int t = threadIdx.x;
+    const int per_window = nsample - 1;
+    const int64_t n_windows = (n_noise + per_window - 1) / per_window;
+    const Philox rng(seed, stream, 0x6e6f6973u /* 'nois' */);
+    uint32_t w4[4];
+    rng.block_at(0, w4);
+    double ar0 = Philox::normal_of(w4, 0);                  // deviate 0: _noise_init, noise_gen.py:84-85
+    for (int64_t w0 = 0; w0 < n_windows; w0 += NM_THREADS) {
+        const int64_t win = w0 + t;
+        __syncthreads();                                    // z and ar_carry of the round before are consumed
+        if (win < n_windows) {
+            // deviates 1 + 10 win .. 10 + 10 win: an odd first index, i.e. the second half of one draw block, four
+            // whole blocks, the first half of a sixth
+            const uint32_t b0 = (uint32_t)((1 + 10 * win) >> 1);
+            rng.block_at(b0, w4);
+            z[t * 10 + 0] = Philox::normal_of(w4, 1);
+#pragma unroll
+            for (int b = 1; b <= 4; b++) {
+                rng.block_at(b0 + b, w4);
+                z[t * 10 + 2 * b - 1] = Philox::normal_of(w4, 0);
+                z[t * 10 + 2 * b] = Philox::normal_of(w4, 1);
+            }
+            rng.block_at(b0 + 5, w4);
+            z[t * 10 + 9] = Philox::normal_of(w4, 0);
+        }
+        __syncthreads();
+        // the chain: ONE thread walks the round's deviates and leaves the chain value in each deviate's slot (all
+        // 128 threads doing it redundantly would saturate the FP64 pipe of an SM that holds sixteen such blocks)
+        const int n_win_round = (int)min((int64_t)NM_THREADS, n_windows - w0);
+        if (t == 0) {
+            // software-pipelined by hand: the ten deviates of the NEXT window are loaded before this window's chain
+            // values are stored over their own deviates, so no load ever waits behind a store to the same array and
+            // the loop runs at the pace of its dependent chain (20 FP64 operations per window)
+            double ar = ar0, zn[10];
+#pragma unroll
+            for (int k = 0; k < 10; k++) zn[k] = z[k];
+            for (int w = 0; w < n_win_round; w++) {
+                double zz[10];
+#pragma unroll
+                for (int k = 0; k < 10; k++) zz[k] = zn[k];
+                if (w + 1 < n_win_round) {
+#pragma unroll
+                    for (int k = 0; k < 10; k++) zn[k] = z[(w + 1) * 10 + k];
+                }
+#pragma unroll
+                for (int k = 0; k < 10; k++) {
+                    ar = ar_next(pacf, ar, zz[k]);          // noise_gen.py:86-88
+                    z[w * 10 + k] = ar;
+                }
+            }
+            *ar_carry = ar;
+        }
+        __syncthreads();
+        const double before = t == 0 ? ar0 : z[t * 10 - 1];
+        if (win < n_windows) {
+            double knots[11];
+            knots[0] = johnson(before, gamma, lambda, delta, xi);           // the knot carried over, noise_gen.py:33-36
+#pragma unroll
+            for (int k = 1; k <= 10; k++) knots[k] = johnson(z[t * 10 + k - 1], gamma, lambda, delta, xi);
+            for (int r = 1; r < nsample; r++) {
+                const int64_t pos = win * per_window + r - 1;
+                if (pos >= n_noise) break;
+                out[pos * n + e] = interp11(sW + r * 11, knots);
+            }
+        }
+        __syncthreads();
+        ar0 = *ar_carry;
+    }
+}
+
 __global__ void __launch_bounds__(NM_THREADS) noise_masked_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
                                                                  const double *W, double pacf, double gamma,
                                                                  double lambda, double delta, double xi, uint64_t seed,
@@ -120,61 +196,32 @@ __global__ void __launch_bounds__(NM_THREADS) noise_masked_kernel(double *out, i
     const int count = n_list;
     if (count == 0) return;
     for (int i = t; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
-    const int per_window = nsample - 1;
-    const int64_t n_windows = (n_noise + per_window - 1) / per_window;
     for (int li = 0; li < count; li++) {                   // (the order inside the list cannot reach a result)
         const int64_t e = (int64_t)blockIdx.x * blockDim.x + list[li];
-        const Philox rng(seed, sel.stream(e), 0x6e6f6973u /* 'nois' */);
-        uint32_t w4[4];
-        rng.block_at(0, w4);
-        double ar0 = Philox::normal_of(w4, 0);              // deviate 0: _noise_init, noise_gen.py:84-85
-        for (int64_t w0 = 0; w0 < n_windows; w0 += NM_THREADS) {
-            const int64_t win = w0 + t;
-            __syncthreads();                                // z and ar_carry of the round before are consumed
-            if (win < n_windows) {
-                // deviates 1 + 10 win .. 10 + 10 win: an odd first index, i.e. the second half of one draw block, four
-                // whole blocks, the first half of a sixth
-                const uint32_t b0 = (uint32_t)((1 + 10 * win) >> 1);
-                rng.block_at(b0, w4);
-                z[t * 10 + 0] = Philox::normal_of(w4, 1);
-#pragma unroll
-                for (int b = 1; b <= 4; b++) {
-                    rng.block_at(b0 + b, w4);
-                    z[t * 10 + 2 * b - 1] = Philox::normal_of(w4, 0);
-                    z[t * 10 + 2 * b] = Philox::normal_of(w4, 1);
-                }
-                rng.block_at(b0 + 5, w4);
-                z[t * 10 + 9] = Philox::normal_of(w4, 0);
-            }
-            __syncthreads();
-            // the chain: ONE thread walks the round's deviates and leaves the chain value in each deviate's slot (all
-            // 128 threads doing it redundantly would saturate the FP64 pipe of an SM that holds sixteen such blocks)
-            const int n_win_round = (int)min((int64_t)NM_THREADS, n_windows - w0);
-            if (t == 0) {
-                double ar = ar0;
-#pragma unroll 10
-                for (int j = 0; j < n_win_round * 10; j++) {
-                    ar = ar_next(pacf, ar, z[j]);               // noise_gen.py:86-88
-                    z[j] = ar;
-                }
-                ar_carry = ar;
-            }
-            __syncthreads();
-            const double before = t == 0 ? ar0 : z[t * 10 - 1];
-            if (win < n_windows) {
-                double knots[11];
-                knots[0] = johnson(before, gamma, lambda, delta, xi);           // the knot carried over, noise_gen.py:33-36
-#pragma unroll
-                for (int k = 1; k <= 10; k++) knots[k] = johnson(z[t * 10 + k - 1], gamma, lambda, delta, xi);
-                for (int r = 1; r < nsample; r++) {
-                    const int64_t pos = win * per_window + r - 1;
-                    if (pos >= n_noise) break;
-                    out[pos * n + e] = interp11(sW + r * 11, knots);
-                }
-            }
-            __syncthreads();
-            ar0 = ar_carry;
-        }
+        noise_episode_by_block(out, n, n_noise, nsample, sW, pacf, gamma, lambda, delta, xi, seed, sel.stream(e), e, z,
+                               &ar_carry);
+    }
+}
+
+// The same for a LIST of episodes gathered over the whole population (sg_vec_finish appends the environments that
+// ended): every block takes listed episodes in turn, so the time of the launch is (listed / resident blocks) episodes
+// instead of the largest number of masked episodes that happen to share a block of 128.
+__global__ void __launch_bounds__(NM_THREADS) noise_listed_kernel(double *out, int64_t n, int64_t n_noise, int nsample,
+                                                                 const double *W, double pacf, double gamma,
+                                                                 double lambda, double delta, double xi, uint64_t seed,
+                                                                 const int64_t *key, const int32_t *list,
+                                                                 const int32_t *count)
+{
+    extern __shared__ double sW[];
+    __shared__ double z[NM_THREADS * 10];
+    __shared__ double ar_carry;
+    const int n_listed = *count;
+    if ((int)blockIdx.x >= n_listed) return;
+    for (int i = threadIdx.x; i < nsample * 11; i += blockDim.x) sW[i] = W[i];
+    for (int li = blockIdx.x; li < n_listed; li += gridDim.x) {
+        const int64_t e = list[li];
+        noise_episode_by_block(out, n, n_noise, nsample, sW, pacf, gamma, lambda, delta, xi, seed, (uint64_t)key[e], e, z,
+                               &ar_carry);
     }
 }
 
@@ -225,6 +272,72 @@ __global__ void __launch_bounds__(128) scenario_kernel(int32_t *meal_minute, dou
 // c = 6 * day + slot consumes the words 6 c .. 6 c + 5 of the Philox stream, so any lane can draw it (Philox::block_at) --
 // and lane 0 then applies the sequential rules (in range, one meal per minute, first wins) in the order of the list.
 // Bit-identical to scenario_kernel (tests/test_gpu_generators.py).
+// One episode's schedule by one warp (see above); cand_m / cand_g: 32 slots of shared memory of this warp.
+__device__ __forceinline__ void scenario_episode_by_warp(int32_t *meal_minute, double *meal_grams, int64_t n, int max_meals,
+                                                         int start_minute, int horizon, uint64_t seed, uint64_t stream,
+                                                         int64_t e, int *cand_m, double *cand_g)
+{
+    const double prob[6] = {0.95, 0.3, 0.95, 0.3, 0.95, 0.3};
+    const double lb[6] = {300, 540, 600, 840, 960, 1200}, ub[6] = {540, 600, 840, 960, 1200, 1380};
+    const double mu[6] = {420, 570, 720, 900, 1080, 1290}, sd[6] = {60, 30, 60, 30, 60, 30};
+    const double amu[6] = {45, 10, 70, 10, 80, 10}, asd[6] = {10, 5, 10, 5, 10, 5};
+    const int lane = threadIdx.x & 31;
+    const Philox rng(seed, stream, 0x6d65616cu /* 'meal' */);
+    const int n_cand = 6 * ((start_minute + horizon + 1439) / 1440);
+    int pos = 0, last = -1;
+    for (int c0 = 0; c0 < n_cand; c0 += 32) {
+        const int c = c0 + lane;
+        int m = INT_MIN;
+        double grams = 0.0;
+        if (c < n_cand) {
+            const int day = c / 6, i = c - 6 * day;
+            // words 6 c .. 6 c + 5 of the stream, handed out from the top of each draw block: (3, 2), (1, 0)
+            uint32_t w0[4], w1[4];
+            const uint32_t b = (uint32_t)((6 * c) >> 2);
+            rng.block_at(b, w0);
+            rng.block_at(b + 1, w1);
+            double u, ut, za;
+            if ((c & 1) == 0) {
+                u = Philox::uniform_of(w0[3], w0[2]); ut = Philox::uniform_of(w0[1], w0[0]);
+                za = normcdfinv(Philox::uniform_of(w1[3], w1[2]));
+            } else {
+                u = Philox::uniform_of(w0[1], w0[0]); ut = Philox::uniform_of(w1[3], w1[2]);
+                za = normcdfinv(Philox::uniform_of(w1[1], w1[0]));
+            }
+            if (u < prob[i]) {
+                const double Fa = normcdf((lb[i] - mu[i]) / sd[i]), Fb = normcdf((ub[i] - mu[i]) / sd[i]);
+                double tt = fma(sd[i], normcdfinv(fma(ut, Fb - Fa, Fa)), mu[i]);
+                tt = fmin(fmax(tt, lb[i]), ub[i]);
+                grams = fmax(rint(fma(asd[i], za, amu[i])), 0.0);
+                m = day * 1440 + (int)rint(tt) - start_minute;
+            }
+        }
+        cand_m[lane] = m;
+        cand_g[lane] = grams;
+        __syncwarp();
+        if (lane == 0) {
+            const int n_here = min(32, n_cand - c0);
+            for (int k = 0; k < n_here; k++) {
+                const int mk = cand_m[k];
+                if (mk == INT_MIN || mk < 0 || mk >= horizon || mk <= last) continue;   // duplicates: first wins
+                const double g = cand_g[k];
+                if (g == 0.0) { last = mk; continue; }                                  // Action(meal=0) is "no meal"
+                if (pos < max_meals) {
+                    meal_minute[(int64_t)pos * n + e] = mk;
+                    meal_grams[(int64_t)pos * n + e] = g;
+                    pos++; last = mk;
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (lane == 0)
+        for (; pos < max_meals; pos++) {
+            meal_minute[(int64_t)pos * n + e] = -1;
+            meal_grams[(int64_t)pos * n + e] = 0.0;
+        }
+}
+
 __global__ void __launch_bounds__(128) scenario_masked_kernel(int32_t *meal_minute, double *meal_grams, int64_t n,
                                                              int max_meals, const int32_t *start_minute_rows,
                                                              int horizon, uint64_t seed, const StreamSel sel)
@@ -245,67 +358,27 @@ __global__ void __launch_bounds__(128) scenario_masked_kernel(int32_t *meal_minu
     if (sel_me) list[base_slot + __popc(ballot & ((1u << lane) - 1u))] = t;
     __syncthreads();
     const int count = n_list;
-    const double prob[6] = {0.95, 0.3, 0.95, 0.3, 0.95, 0.3};
-    const double lb[6] = {300, 540, 600, 840, 960, 1200}, ub[6] = {540, 600, 840, 960, 1200, 1380};
-    const double mu[6] = {420, 570, 720, 900, 1080, 1290}, sd[6] = {60, 30, 60, 30, 60, 30};
-    const double amu[6] = {45, 10, 70, 10, 80, 10}, asd[6] = {10, 5, 10, 5, 10, 5};
     for (int li = warp; li < count; li += 4) {
         const int64_t e = (int64_t)blockIdx.x * blockDim.x + list[li];
-        const int start_minute = start_minute_rows[e];
-        const Philox rng(seed, sel.stream(e), 0x6d65616cu /* 'meal' */);
-        const int n_cand = 6 * ((start_minute + horizon + 1439) / 1440);
-        int pos = 0, last = -1;
-        for (int c0 = 0; c0 < n_cand; c0 += 32) {
-            const int c = c0 + lane;
-            int m = INT_MIN;
-            double grams = 0.0;
-            if (c < n_cand) {
-                const int day = c / 6, i = c - 6 * day;
-                // words 6 c .. 6 c + 5 of the stream, handed out from the top of each draw block: (3, 2), (1, 0)
-                uint32_t w0[4], w1[4];
-                const uint32_t b = (uint32_t)((6 * c) >> 2);
-                rng.block_at(b, w0);
-                rng.block_at(b + 1, w1);
-                double u, ut, za;
-                if ((c & 1) == 0) {
-                    u = Philox::uniform_of(w0[3], w0[2]); ut = Philox::uniform_of(w0[1], w0[0]);
-                    za = normcdfinv(Philox::uniform_of(w1[3], w1[2]));
-                } else {
-                    u = Philox::uniform_of(w0[1], w0[0]); ut = Philox::uniform_of(w1[3], w1[2]);
-                    za = normcdfinv(Philox::uniform_of(w1[1], w1[0]));
-                }
-                if (u < prob[i]) {
-                    const double Fa = normcdf((lb[i] - mu[i]) / sd[i]), Fb = normcdf((ub[i] - mu[i]) / sd[i]);
-                    double tt = fma(sd[i], normcdfinv(fma(ut, Fb - Fa, Fa)), mu[i]);
-                    tt = fmin(fmax(tt, lb[i]), ub[i]);
-                    grams = fmax(rint(fma(asd[i], za, amu[i])), 0.0);
-                    m = day * 1440 + (int)rint(tt) - start_minute;
-                }
-            }
-            cand_m[warp][lane] = m;
-            cand_g[warp][lane] = grams;
-            __syncwarp();
-            if (lane == 0) {
-                const int n_here = min(32, n_cand - c0);
-                for (int k = 0; k < n_here; k++) {
-                    const int mk = cand_m[warp][k];
-                    if (mk == INT_MIN || mk < 0 || mk >= horizon || mk <= last) continue;   // duplicates: first wins
-                    const double g = cand_g[warp][k];
-                    if (g == 0.0) { last = mk; continue; }                                  // Action(meal=0) is "no meal"
-                    if (pos < max_meals) {
-                        meal_minute[(int64_t)pos * n + e] = mk;
-                        meal_grams[(int64_t)pos * n + e] = g;
-                        pos++; last = mk;
-                    }
-                }
-            }
-            __syncwarp();
-        }
-        if (lane == 0)
-            for (; pos < max_meals; pos++) {
-                meal_minute[(int64_t)pos * n + e] = -1;
-                meal_grams[(int64_t)pos * n + e] = 0.0;
-            }
+        scenario_episode_by_warp(meal_minute, meal_grams, n, max_meals, start_minute_rows[e], horizon, seed, sel.stream(e),
+                                 e, cand_m[warp], cand_g[warp]);
+    }
+}
+
+// The same for a LIST of episodes gathered over the whole population: one warp per listed episode.
+__global__ void __launch_bounds__(128) scenario_listed_kernel(int32_t *meal_minute, double *meal_grams, int64_t n,
+                                                             int max_meals, const int32_t *start_minute_rows,
+                                                             int horizon, uint64_t seed, const int64_t *key,
+                                                             const int32_t *list, const int32_t *count)
+{
+    __shared__ int cand_m[4][32];
+    __shared__ double cand_g[4][32];
+    const int warp = threadIdx.x >> 5;
+    const int n_listed = *count;
+    for (int li = blockIdx.x * 4 + warp; li < n_listed; li += gridDim.x * 4) {
+        const int64_t e = list[li];
+        scenario_episode_by_warp(meal_minute, meal_grams, n, max_meals, start_minute_rows[e], horizon, seed,
+                                 (uint64_t)key[e], e, cand_m[warp], cand_g[warp]);
     }
 }
 
@@ -372,7 +445,7 @@ __global__ void __launch_bounds__(256) vec_finish_kernel(const double *row, int6
                                                         int32_t *episode_steps, int32_t horizon,
                                                         const int64_t *episodes_started, int64_t env0, int64_t group,
                                                         int key_shift, int32_t *mask, int64_t *key, double *terminal_obs,
-                                                        uint8_t *done, uint8_t *truncated)
+                                                        uint8_t *done, uint8_t *truncated, int32_t *list, int32_t *count)
 {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
@@ -385,6 +458,7 @@ __global__ void __launch_bounds__(256) vec_finish_kernel(const double *row, int6
     terminal_obs[e] = row[(int64_t)obs_row * n + e];
     done[e] = d ? 1 : 0;
     truncated[e] = (fin && !d) ? 1 : 0;
+    if (fin && list) list[atomicAdd(count, 1)] = (int32_t)e;     // (the order of the list cannot reach a result)
 }
 
 __global__ void __launch_bounds__(256) vec_restart_kernel(const int32_t *mask, int64_t n, int64_t *episodes_started,
@@ -400,6 +474,8 @@ __global__ void __launch_bounds__(256) vec_restart_kernel(const int32_t *mask, i
     }
     obs_out[e] = fin ? obs_new[e] : obs_step[e];
 }
+
+constexpr int LISTED_BLOCKS = 148 * 16;    // one resident wave of 128-thread blocks: the listed kernels stride over their list
 
 inline unsigned blocks(int64_t n, int b) { return (unsigned)((n + b - 1) / b); }
 
@@ -464,6 +540,33 @@ int sg_gen_scenarios_keyed(int32_t *meal_minute, double *meal_grams, int64_t n_e
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 
+int sg_gen_noise_listed(double *out, int64_t n_episodes, int64_t n_noise, int32_t nsample, const double *W_dev,
+                        const double *model_host, uint64_t seed, const int64_t *key, const int32_t *list,
+                        const int32_t *count, void *stream)
+{
+    if (!out || !W_dev || !model_host || !key || !list || !count || n_episodes <= 0 || n_noise <= 0 || nsample < 2 ||
+        nsample * 11 > MAX_W)
+        return SG_ERR_ARG;
+    const unsigned grid = (unsigned)std::min((int64_t)LISTED_BLOCKS, n_episodes);
+    noise_listed_kernel<<<grid, NM_THREADS, sizeof(double) * nsample * 11, (cudaStream_t)stream>>>(
+        out, n_episodes, n_noise, nsample, W_dev, model_host[0], model_host[1], model_host[2], model_host[3],
+        model_host[4], seed, key, list, count);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
+int sg_gen_scenarios_listed(int32_t *meal_minute, double *meal_grams, int64_t n_episodes, int32_t max_meals,
+                            const int32_t *start_minute, int32_t horizon_minutes, uint64_t seed, const int64_t *key,
+                            const int32_t *list, const int32_t *count, void *stream)
+{
+    if (!meal_minute || !meal_grams || !start_minute || !key || !list || !count || n_episodes <= 0 || max_meals <= 0 ||
+        horizon_minutes <= 0)
+        return SG_ERR_ARG;
+    const unsigned grid = (unsigned)std::min((int64_t)LISTED_BLOCKS, (n_episodes + 3) / 4);
+    scenario_listed_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(meal_minute, meal_grams, n_episodes, max_meals,
+                                                                   start_minute, horizon_minutes, seed, key, list, count);
+    return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
+}
+
 int sg_gen_episode_starts(int32_t *start_minute, double *x0, const double *table_x0_dev, const int32_t *patient_row,
                           int64_t n_episodes, int32_t n_draws, uint64_t seed, const int64_t *key, const int32_t *mask,
                           void *stream)
@@ -495,14 +598,16 @@ int sg_gen_uniform(double *out, int64_t n, double lo, double hi, uint64_t seed, 
 int sg_vec_finish(const double *row, int64_t n_envs, int32_t done_row, int32_t obs_row, int32_t *episode_steps,
                   int32_t horizon_steps, const int64_t *episodes_started, int64_t env_offset, int64_t group_size,
                   int32_t key_shift, int32_t *mask, int64_t *key, double *terminal_obs, uint8_t *done, uint8_t *truncated,
-                  void *stream)
+                  int32_t *list, int32_t *count, void *stream)
 {
     if (!row || !episode_steps || !episodes_started || !mask || !key || !terminal_obs || !done || !truncated ||
-        n_envs <= 0 || group_size < 1 || key_shift < 1 || key_shift > 40 || done_row < 0 || obs_row < 0)
+        n_envs <= 0 || n_envs > INT32_MAX || group_size < 1 || key_shift < 1 || key_shift > 40 || done_row < 0 ||
+        obs_row < 0 || (list != nullptr) != (count != nullptr))
         return SG_ERR_ARG;
+    if (count && cudaMemsetAsync(count, 0, sizeof(int32_t), (cudaStream_t)stream) != cudaSuccess) return SG_ERR_CUDA;
     vec_finish_kernel<<<blocks(n_envs, 256), 256, 0, (cudaStream_t)stream>>>(
         row, n_envs, done_row, obs_row, episode_steps, horizon_steps, episodes_started, env_offset, group_size, key_shift,
-        mask, key, terminal_obs, done, truncated);
+        mask, key, terminal_obs, done, truncated, list, count);
     return cudaGetLastError() == cudaSuccess ? SG_OK : SG_ERR_CUDA;
 }
 

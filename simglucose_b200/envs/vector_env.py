@@ -119,6 +119,8 @@ class T1DSimVecEnv(object):
         self._terminal_obs = torch.zeros(E, dtype=torch.float64, device=dev)
         self._done = torch.zeros(E, dtype=torch.bool, device=dev)
         self._truncated = torch.zeros(E, dtype=torch.bool, device=dev)
+        self._list = torch.zeros(E, dtype=torch.int32, device=dev)          # the environments that ended, gathered
+        self._count = torch.zeros(1, dtype=torch.int32, device=dev)
         if self.stream_mode == 'reference' and self.gym_seeding:
             # one gym np_random per environment (simglucose_gym_env.py:38); the wrapper's constructor already builds
             # one env from it (:39), which consumes the first chain of draws
@@ -137,9 +139,10 @@ class T1DSimVecEnv(object):
         hour = rng.randint(low=0.0, high=24.0)
         return int(seed2), int(seed3), int(seed4), int(hour)
 
-    def _new_episodes_device(self, mask, key=None):
+    def _new_episodes_device(self, mask, key=None, listed=None):
         """Philox streams for the environments in mask (int32 [E] device tensor, None = all), no host involvement.
-        key: the stream keys when the caller already has them (sg_vec_finish)."""
+        key / listed: the stream keys and the gathered list of the masked environments when the caller already has
+        them (sg_vec_finish)."""
         if key is None:
             key = (self._env_index // self.group_size << _KEY_SHIFT) | self.episodes_started
         x0 = None
@@ -147,9 +150,9 @@ class T1DSimVecEnv(object):
             S.device_episode_starts(key, self.patient_row, self._table_x0, n_draws=2, seed=self.seed, mask=mask,
                                     start_minute=self.start_minutes, x0=self._x0_buf)
             x0 = self._x0_buf
-        S.device_noise_keyed(self._noise, key, self.engine.sensor, seed=self.seed, mask=mask, W=self._W)
+        S.device_noise_keyed(self._noise, key, self.engine.sensor, seed=self.seed, mask=mask, W=self._W, listed=listed)
         S.device_scenarios_keyed(self._mm, self._mg, self.start_minutes, self.horizon_steps * self.sample_time, key,
-                                 seed=self.seed, mask=mask)
+                                 seed=self.seed, mask=mask, listed=listed)
         return x0
 
     def _new_episodes_reference(self, idx):
@@ -271,6 +274,7 @@ class T1DSimVecEnv(object):
                                           self.horizon_steps, self.episodes_started.data_ptr(), self.episode_offset,
                                           self.group_size, _KEY_SHIFT, self._mask.data_ptr(), self._key.data_ptr(),
                                           self._terminal_obs.data_ptr(), self._done.data_ptr(), self._truncated.data_ptr(),
+                                          self._list.data_ptr(), self._count.data_ptr(),
                                           torch.cuda.current_stream(self.device).cuda_stream))
             done = self._done
         else:
@@ -293,7 +297,7 @@ class T1DSimVecEnv(object):
             mask = self._mask                                              # filled by sg_vec_finish
             self.info['terminal_obs'] = self._terminal_obs
             self.info['truncated'] = self._truncated
-            x0 = self._new_episodes_device(mask, key=self._key)
+            x0 = self._new_episodes_device(mask, key=self._key, listed=(self._list, self._count))
             self.engine.reset_masked(mask, x0=self._x0_for_reset(x0), row0=self._row0)
             if self.cgm_window is not None:
                 finished = mask != 0

@@ -308,10 +308,12 @@ def _noise_model(s):
     return (C.c_double * 5)(s['PACF'], s['gamma'], s['lambda'], s['delta'], s['xi'])
 
 
-def device_noise_keyed(out, key, sensor='Dexcom', seed=0, mask=None, W=None):
+def device_noise_keyed(out, key, sensor='Dexcom', seed=0, mask=None, W=None, listed=None):
     """Rewrite columns of the noise buffer out [n_noise, E] in place: episode e draws the Philox stream named by
     key[e] (int64 device tensor); only columns with mask[e] != 0 (int32 device tensor, None = all) are written.
-    W: the device copy of interp_matrix(sample_time), for callers that generate every step (no upload, no sync)."""
+    W: the device copy of interp_matrix(sample_time), for callers that generate every step (no upload, no sync).
+    listed = (list [E] int32, count [1] int32) device tensors: write the columns list[0 .. count) instead (what
+    sg_vec_finish gathers; sg_gen_noise_listed) -- same streams."""
     import torch
     from . import _capi
     lib = _capi.load()
@@ -321,6 +323,13 @@ def device_noise_keyed(out, key, sensor='Dexcom', seed=0, mask=None, W=None):
     if own_W:
         W = torch.from_numpy(interp_matrix(s['sample_time'])).to(dev)
     assert out.is_contiguous() and key.dtype == torch.int64 and (mask is None or mask.dtype == torch.int32)
+    if listed is not None:
+        assert not own_W and listed[0].dtype == torch.int32 and listed[1].dtype == torch.int32
+        with torch.cuda.device(dev):
+            _capi.check(lib.sg_gen_noise_listed(C.c_void_p(out.data_ptr()), out.shape[1], out.shape[0], W.shape[0],
+                                                C.c_void_p(W.data_ptr()), _noise_model(s), seed, C.c_void_p(key.data_ptr()),
+                                                C.c_void_p(listed[0].data_ptr()), C.c_void_p(listed[1].data_ptr()), _stream()))
+        return out
     with torch.cuda.device(dev):
         _capi.check(lib.sg_gen_noise_keyed(C.c_void_p(out.data_ptr()), out.shape[1], out.shape[0], W.shape[0],
                                            C.c_void_p(W.data_ptr()), _noise_model(s), seed, C.c_void_p(key.data_ptr()),
@@ -330,13 +339,22 @@ def device_noise_keyed(out, key, sensor='Dexcom', seed=0, mask=None, W=None):
     return out
 
 
-def device_scenarios_keyed(meal_minute, meal_grams, start_minute, horizon_minutes, key, seed=0, mask=None):
+def device_scenarios_keyed(meal_minute, meal_grams, start_minute, horizon_minutes, key, seed=0, mask=None, listed=None):
     """Rewrite columns of the meal table (meal_minute / meal_grams [M, E]) in place: RandomScenario-distributed meals
-    of an episode that starts at minute-of-day start_minute[e] (int32 device tensor); stream key[e], columns mask[e]."""
+    of an episode that starts at minute-of-day start_minute[e] (int32 device tensor); stream key[e], columns mask[e]
+    -- or the columns list[0 .. count) with listed = (list, count) (sg_gen_scenarios_listed)."""
     import torch
     from . import _capi
     lib = _capi.load()
     assert meal_minute.is_contiguous() and meal_grams.is_contiguous() and start_minute.dtype == torch.int32
+    if listed is not None:
+        with torch.cuda.device(meal_minute.device):
+            _capi.check(lib.sg_gen_scenarios_listed(C.c_void_p(meal_minute.data_ptr()), C.c_void_p(meal_grams.data_ptr()),
+                                                    meal_minute.shape[1], meal_minute.shape[0],
+                                                    C.c_void_p(start_minute.data_ptr()), int(horizon_minutes), seed,
+                                                    C.c_void_p(key.data_ptr()), C.c_void_p(listed[0].data_ptr()),
+                                                    C.c_void_p(listed[1].data_ptr()), _stream()))
+        return meal_minute, meal_grams
     with torch.cuda.device(meal_minute.device):
         _capi.check(lib.sg_gen_scenarios_keyed(C.c_void_p(meal_minute.data_ptr()), C.c_void_p(meal_grams.data_ptr()),
                                                meal_minute.shape[1], meal_minute.shape[0],

@@ -28,7 +28,7 @@ def _acf(x, lag):
 def test_device_noise_matches_cgmnoise_distribution(sensor):
     import torch
     from scipy import stats
-    from simglucose_b200 import streams as S
+    from simglucose_b200 import params as P, streams as S
     L, E_dev, E_host = 256, 4096, 384                       # 2^20 device samples; 98,304 host samples per sensor
     dev = S.device_noise(E_dev, L, sensor, seed=12345, group_size=1).cpu().numpy().T          # [E, L]
     host = np.stack([S.cgm_noise_stream(sensor, 1000 + s, L) for s in range(E_host)])
@@ -68,6 +68,18 @@ def test_device_noise_matches_cgmnoise_distribution(sensor):
     assert torch.equal(part[:, m], full[:, m]) and bool((part[:, ~m] == -1.0).all())
     ones = torch.ones(1000, dtype=torch.int32, device='cuda')
     assert torch.equal(S.device_noise_keyed(torch.zeros_like(full), key, sensor, seed=3, mask=ones), full)
+    # ... and so does the kernel that works through a gathered LIST of episodes (any order, count read on the device)
+    idx = m.nonzero().reshape(-1).to(torch.int32)
+    lst = torch.zeros(1000, dtype=torch.int32, device='cuda')
+    lst[:idx.numel()] = idx[torch.randperm(idx.numel(), device='cuda')]
+    cnt = torch.tensor([idx.numel()], dtype=torch.int32, device='cuda')
+    W = torch.from_numpy(S.interp_matrix(P.sensor_params(sensor)['sample_time'])).cuda()
+    lp = S.device_noise_keyed(torch.full((L + 3, 1000), -1.0, dtype=torch.float64, device='cuda'), key, sensor, seed=3, W=W,
+                              listed=(lst, cnt))
+    assert torch.equal(lp[:, m], full[:, m]) and bool((lp[:, ~m] == -1.0).all())
+    none = S.device_noise_keyed(torch.full((L + 3, 1000), -1.0, dtype=torch.float64, device='cuda'), key, sensor, seed=3, W=W,
+                                listed=(lst, torch.zeros(1, dtype=torch.int32, device='cuda')))
+    assert bool((none == -1.0).all())
 
 
 _PROB = [0.95, 0.3, 0.95, 0.3, 0.95, 0.3]                   # scenario_gen.py:38-44
@@ -163,6 +175,15 @@ def test_device_scenarios_match_random_scenario_distribution():
         allm = S.device_scenarios_keyed(torch.zeros_like(full[0]), torch.zeros_like(full[1]), starts, horizon, key, seed=21, mask=ones)
         assert torch.equal(allm[0], full[0]) and torch.equal(allm[1], full[1])
         assert int((full[0] >= 0).sum()) > n * (horizon // 480)                                # the tables are not empty
+        idx = mb.nonzero().reshape(-1).to(torch.int32)
+        lst = torch.zeros(n, dtype=torch.int32, device='cuda')
+        lst[:idx.numel()] = idx[torch.randperm(idx.numel(), device='cuda')]
+        cnt = torch.tensor([idx.numel()], dtype=torch.int32, device='cuda')
+        lp = S.device_scenarios_keyed(torch.full((M, n), -7, dtype=torch.int32, device='cuda'),
+                                      torch.full((M, n), -7.0, dtype=torch.float64, device='cuda'), starts, horizon, key, seed=21,
+                                      listed=(lst, cnt))
+        assert torch.equal(lp[0][:, mb], full[0][:, mb]) and torch.equal(lp[1][:, mb], full[1][:, mb])
+        assert bool((lp[0][:, ~mb] == -7).all()) and bool((lp[1][:, ~mb] == -7.0).all())
     # the host table builder and the device kernel agree on how a schedule becomes a table (start 00:00, 1 day)
     hm, hg = S.random_scenario_table(3, 0, 1440)
     assert np.all(np.diff(hm) > 0) and np.all(hg > 0)
