@@ -43,5 +43,18 @@ class CustomScenario(Scenario):
                 return Action(meal=grams)
         return Action(meal=0)
 
+    def meal_table(self, first_minute, n_minutes):
+        """get_action for the minutes first_minute .. first_minute + n_minutes - 1 after start_time as (minutes, grams)
+        of the non-zero meals (first matching entry wins, like the loop above)."""
+        import numpy as np
+        first = {}
+        for when, grams in (self.scenario or []):
+            sec = (parseTime(when, self.start_time) - self.start_time).total_seconds()
+            if sec == int(sec) and int(sec) % 60 == 0:         # get_action is asked on whole minutes after start_time
+                first.setdefault(int(sec) // 60, grams)
+        lo, hi = int(first_minute), int(first_minute) + int(n_minutes)
+        keep = sorted(m for m, g in first.items() if lo <= m < hi and g != 0)
+        return np.array(keep, dtype=np.int32), np.array([float(first[m]) for m in keep], dtype=np.float64)
+
     def reset(self):
         pass

@@ -32,6 +32,15 @@ def _n_steps(env, sim_time):
 
 def _meal_table(env, n_minutes):
     """Replay scenario.get_action once per episode minute, as env.mini_step would (env.py:50)."""
+    sc = env.scenario
+    # this package's own scenario classes build the same table (and leave the same generator state) day by day
+    from .scenario import CustomScenario
+    from .scenario_gen import RandomScenario
+    for cls in (RandomScenario, CustomScenario):
+        if isinstance(sc, cls) and type(sc).get_action is cls.get_action:
+            fast = sc.meal_table(env.patient.t0, n_minutes)
+            if fast is not None:
+                return fast
     start = env.scenario.start_time
     mm, gg = [], []
     for m in range(int(n_minutes)):

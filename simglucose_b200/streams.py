@@ -98,12 +98,13 @@ def cgm_noise_stream(sensor, seed, n):
     t15 = np.array(range(0, PRECOMPUTE + 1)) * MDL_SAMPLE_TIME
     t = np.array(range(0, nsample)) * st
     W = None if interp1d is not None else interp_matrix(st)
-    out = []
-    for w in range(n_windows):
-        knots = eps[w * PRECOMPUTE: w * PRECOMPUTE + PRECOMPUTE + 1]
-        vals = interp1d(t15, knots, kind='cubic')(t) if interp1d is not None else W @ knots
-        out.append(vals[1:])
-    return np.concatenate(out)[:int(n)]
+    # all windows at once: knots [11, n_windows]; scipy's spline solve treats the columns independently, and the result
+    # equals the reference's one interp1d per window bit for bit (checked by tests/test_host_logic.py against streams
+    # recorded from the reference)
+    idx = np.arange(PRECOMPUTE + 1)[:, None] + PRECOMPUTE * np.arange(n_windows)[None, :]
+    knots = eps[idx]
+    vals = interp1d(t15, knots, kind='cubic', axis=0)(t) if interp1d is not None else W @ knots     # [nsample, n_windows]
+    return vals[1:].T.reshape(-1)[:int(n)]
 
 
 # ---------------------------------------------------------------------------------------------

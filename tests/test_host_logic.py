@@ -228,3 +228,37 @@ def test_stats_allreduce_over_gloo_world_size_2(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert 'rank 0 ok' in r.stdout and 'rank 1 ok' in r.stdout
+
+
+def test_scenario_meal_tables_equal_the_per_minute_replay():
+    """batch_sim's fused path asks this package's scenario classes for their meal table (one loop turn per calendar day)
+    instead of calling get_action once per simulated minute as env.mini_step does (env.py:50): same meals, same
+    generator state and current-day schedule afterwards (scenario_gen.py:15-31, scenario.py:33-42)."""
+    from datetime import datetime, timedelta
+    from simglucose_b200.simulation.scenario import CustomScenario
+    from simglucose_b200.simulation.scenario_gen import RandomScenario
+
+    def replay(sc, t0, n):
+        mm, gg = [], []
+        for m in range(n):
+            g = sc.get_action(sc.start_time + timedelta(minutes=t0 + m)).meal
+            if g != 0:
+                mm.append(m + t0)
+                gg.append(float(g))
+        return np.array(mm, dtype=np.int32), np.array(gg)
+
+    for seed in range(3):
+        for start in (datetime(2018, 1, 1, 0, 0, 0), datetime(2018, 1, 1, 6, 30, 0), datetime(2018, 1, 1, 23, 59, 0)):
+            for t0, n in ((0, 4320), (5, 1440), (1000, 3000)):
+                a, b = RandomScenario(start_time=start, seed=seed), RandomScenario(start_time=start, seed=seed)
+                want, got = replay(a, t0, n), b.meal_table(t0, n)
+                assert np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1])
+                assert a.scenario == b.scenario and a.random_gen.randint(1 << 30) == b.random_gen.randint(1 << 30)
+    assert RandomScenario(start_time=datetime(2018, 1, 1, 0, 0, 30), seed=1).meal_table(0, 10) is None
+    start = datetime(2018, 1, 1, 0, 0, 0)
+    entries = [(7, 45), (12, 70), (16, 15), (18, 80), (23, 10), (7, 99), (timedelta(hours=30), 33),
+               (datetime(2018, 1, 1, 9, 30), 5), (1.004, 8), (2, 0)]
+    c = CustomScenario(start_time=start, scenario=entries)
+    for t0, n in ((0, 1440), (0, 2880), (600, 500)):
+        want, got = replay(c, t0, n), c.meal_table(t0, n)
+        assert np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1])
