@@ -25,8 +25,10 @@ pathos = False     # kept for scripts that inspect it: the GPU batch replaces th
 
 
 def _n_steps(env, sim_time):
-    """Env-steps taken by `while env.time < start + sim_time` (sim_engine.py:33)."""
-    minutes = sim_time.total_seconds() / 60.0
+    """Env-steps taken by `while env.time < start + sim_time` (sim_engine.py:33): env.time is start_time plus the
+    patient's clock, which starts at T1DPatient(t0=...) (env.py:44-46, t1dpatient.py:27), so an episode that starts
+    late takes ceil((minutes - t0) / sample_time) steps."""
+    minutes = sim_time.total_seconds() / 60.0 - float(getattr(env.patient, 't0', 0))
     return max(0, int(np.ceil(minutes / float(env.sample_time))))
 
 
