@@ -86,6 +86,15 @@ def g_custom(pool):
     _save('custom_scenario', pool.map(_episode, jobs))
 
 
+def g_late_start(pool):
+    """T1DPatient(t0=...) (patient/t1dpatient.py:27, 277): the patient's clock -- and with it env.time, the meal lookup
+    and the sensor's sampling minute (cgm.py:27) -- starts late.  t0 = 3 keeps the sampling phase, t0 = 1 and 2 shift it:
+    the reset then returns the sensor's held 0 (cgm.py:47-50) and the noise stream is consumed from its first sample."""
+    jobs = [(n, 160, dict(controller=('bb', 140.0), scenario=('custom', CUSTOM), start_hour=6, sensor_seed=4, t0=t0))
+            for n, t0 in (('adult#002', 1), ('child#005', 2), ('adolescent#003', 3), ('adult#009', 7))]
+    _save('late_start', pool.map(_episode, jobs))
+
+
 def g_cohort_bb(pool):
     """BASELINE.json configs[1]: all 30 patients x 3 days, RandomScenario seed 1, BBController."""
     names = H.patient_names()
@@ -240,7 +249,7 @@ def g_generator_samples(pool):
 
 GROUPS = dict(golden_config=g_golden_config, custom=g_custom, cohort_bb=g_cohort_bb, cohort_pid=g_cohort_pid,
               open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise, report=g_report,
-              generator_samples=g_generator_samples)
+              generator_samples=g_generator_samples, late_start=g_late_start)
 
 if __name__ == '__main__':
     groups = sys.argv[1:] or list(GROUPS)

@@ -74,7 +74,7 @@ def noise_stream(sensor_name, seed, n):
 
 def run_episode(patient_name, n_steps, controller=('bb', 140.0), scenario=('random', 1),
                 start_hour=0, sensor_name='Dexcom', sensor_seed=1, pump_name='Insulet',
-                actions=None, random_init_bg=False, patient_seed=None):
+                actions=None, random_init_bg=False, patient_seed=None, t0=0):
     """Run the reference closed loop for n_steps env-steps exactly as
     SimObj.simulate does (simulation/sim_engine.py:29-39), recording inputs and
     outputs.
@@ -94,7 +94,7 @@ def run_episode(patient_name, n_steps, controller=('bb', 140.0), scenario=('rand
     from simglucose.simulation.scenario import CustomScenario
 
     start_time = datetime(2018, 1, 1, start_hour, 0, 0)
-    patient = make_patient(patient_name, random_init_bg=random_init_bg, seed=patient_seed)
+    patient = make_patient(patient_name, random_init_bg=random_init_bg, seed=patient_seed, t0=t0)
     sensor = CGMSensor.withName(sensor_name, seed=sensor_seed)
     pump = InsulinPump.withName(pump_name)
     if scenario[0] == 'random':
@@ -160,6 +160,7 @@ def run_episode(patient_name, n_steps, controller=('bb', 140.0), scenario=('rand
         patient_row=np.int32(csv_row),
         sample_time=np.int32(sample_time),
         start_minute=np.int32(start_hour * 60),
+        t0=np.int32(t0),
         n_steps=np.int32(n_steps),
         x0=x0,
         meal_minute=np.array([m for m, _ in meals], dtype=np.int32),

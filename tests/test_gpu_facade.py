@@ -81,6 +81,38 @@ def test_env_loop_with_host_controller_matches_reference():
     assert env.patient.t == 3.0 * int(d['n_steps'][i])
 
 
+def test_late_start_t0_matches_reference():
+    """T1DPatient(t0=...) (t1dpatient.py:27, 277): the patient's clock starts late, and with it env.time, the meal lookup
+    and the sensor's sampling minute.  Fixtures recorded from the reference with t0 = 1, 2, 3, 7: for t0 % sample_time != 0
+    the reset returns the sensor's held 0 and consumes no noise (cgm.py:27, 47-50).  Both seams: the loop with the host
+    controller, and SimObj.simulate's fused launch, whose step count is ceil((minutes - t0) / sample_time)."""
+    from simglucose_b200.controller.basal_bolus_ctrller import BBController
+    from simglucose_b200.simulation.sim_engine import SimObj, _n_steps
+    d = H.load('late_start')
+    for i in range(len(d['t0'])):
+        t0, n = int(d['t0'][i]), int(d['n_steps'][i])
+        name = _names()[int(d['patient_row'][i])]
+        env = _build_env(name, 6, 4, ('custom', CUSTOM), t0=t0)
+        ctrl = BBController(target=140)
+        ctrl.reset()
+        obs, reward, done, info = env.reset()
+        obs_l = [obs.CGM]
+        for _ in range(n):
+            obs, reward, done, info = env.step(ctrl.policy(obs, reward, done, **info))
+            obs_l.append(obs.CGM)
+        assert env.time == datetime(2018, 1, 1, 6) + timedelta(minutes=t0 + 3 * n) and env.patient.t == t0 + 3.0 * n
+        _check_frame(env.show_history(), d, i)
+        assert obs_l[0] == d['obs'][i][0] and H.rel_err(obs_l, d['obs'][i]) <= TOL
+        assert H.rel_err(env.patient.state, d['final_state'][i]) <= TOL
+        # the fused episode: sim_time chosen so that the reference's loop takes exactly n steps
+        env2 = _build_env(name, 6, 4, ('custom', CUSTOM), t0=t0)
+        sim_time = timedelta(minutes=t0 + 3 * n - 1)
+        assert _n_steps(env2, sim_time) == n
+        s = SimObj(env2, BBController(target=140), sim_time, animate=False, path=None)
+        s.simulate()
+        _check_frame(s.results(), d, i)
+
+
 def test_batch_sim_fused_matches_reference_and_writes_csv(tmp_path):
     """batch_sim over SimObj's (sim_engine.py:65-76): BB controllers fuse into one episode launch."""
     import pandas as pd

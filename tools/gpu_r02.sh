@@ -26,11 +26,19 @@ timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_d
   --log-file $OUT/run_kernel_dram_traffic.csv python bench.py --steps 1 --warmup 1 --no-cpu --no-e2e --no-configs > $OUT/ncu_traffic.log 2>&1
 echo "ncu traffic rc=$?" | tee -a $OUT/rc.txt
 if [[ " $* " != *" noconfigs "* ]]; then
-  timeout 1500 python tools/bench_configs.py --only 2,4 > $OUT/configs.jsonl 2> $OUT/configs.err; echo "configs rc=$?" | tee -a $OUT/rc.txt
+  timeout 1500 python tools/bench_configs.py --only 2,3,4 > $OUT/configs.jsonl 2> $OUT/configs.err; echo "configs rc=$?" | tee -a $OUT/rc.txt
+fi
+if [[ " $* " == *" modes "* ]]; then      # the other arithmetic modes, for the record (never the default)
+  for m in "--fma" "--carry-h" "--carry-h --fma" "--fp32"; do
+    f=$(echo "$m" | tr -d ' -' | sed 's/^$/default/')
+    timeout 600 python bench.py --no-cpu --no-configs --no-traces $m > $OUT/bench_$f.json 2> $OUT/bench_$f.err; echo "bench $m rc=$?" | tee -a $OUT/rc.txt
+  done
+  timeout 600 python bench.py --impl reference --carry-h --steps 2 --warmup 1 --no-ref-python > $OUT/bench_reference_carryh.json 2> $OUT/bench_reference_carryh.err
 fi
 python - <<PY
 import json
-for f in ('bench.json','bench_reference.json','prof_plain.log'):
+import glob, os
+for f in ['bench.json','bench_reference.json','prof_plain.log'] + sorted(os.path.basename(x) for x in glob.glob('$OUT/bench_*.json') if 'reference.json' not in x):
     try:
         d=json.loads(open('$OUT/'+f).read().strip().split('\n')[-1])
         r=d.get('roofline') or {}
