@@ -727,34 +727,37 @@ def main():
                'shards': n_sh, 'coherence_steps': coherence_e2e, 'rows_check': float(e2e_agg[0][0])}
         # ---- the same with the trajectories copied out: BG, CGM, CHO, insulin of every env-step (the columns of the
         # reference's result DataFrame, sim_engine.py:44-49) into pinned host memory, for the first shards ----
-        if not args.no_traces:
-            n_tr = min(n_sh, 3)
-            tr_h = [torch.empty(n_steps, 4, hi - lo, dtype=torch.float64).pin_memory()
-                    for lo, hi in zip(cuts[:n_tr], cuts[1:n_tr + 1])]
-            ep_tr = cuts[n_tr] - cuts[0]
+        if not args.no_traces and world == 1:
+            try:
+                n_tr = min(n_sh, 3)
+                tr_h = [torch.empty(n_steps, 4, hi - lo, dtype=torch.float64).pin_memory()
+                        for lo, hi in zip(cuts[:n_tr], cuts[1:n_tr + 1])]
+                ep_tr = cuts[n_tr] - cuts[0]
 
-            def tr_pass():
-                runner.run(shards[:n_tr], n_steps, controller='bb', stats_out=stats_h[:n_tr], traces_out=tr_h)
-                torch.cuda.synchronize()
-            tr_pass()
-            barrier()
-            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0.record()
-            tr_pass()
-            t1.record()
-            barrier()
-            ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
-            if world > 1:
-                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-            e2e['traces'] = {'value': world * ep_tr * n_min / (float(ms.item()) * 1e-3), 'unit': METRIC,
-                             'episodes_per_gpu': ep_tr, 'shards': n_tr, 'columns': ['BG', 'CGM', 'CHO', 'insulin'],
-                             'h2d_bytes': int(sum(v.numel() * v.element_size() for sh in shards[:n_tr] for v in sh.values())),
-                             'd2h_bytes': int(sum(t.numel() * 8 for t in tr_h) + sum(t.numel() * 8 for t in stats_h[:n_tr])),
-                             'what': 'ShardRunner.run(traces_out=...): host inputs in, per-episode statistics AND the '
-                                     'trajectories (one row per env-step) out, device -> host copy overlapped with the '
-                                     'next shard; bounded to the first %d shards' % n_tr,
-                             'bg_check': float(tr_h[0][-1, 0].mean())}
-            del tr_h
+                def tr_pass():
+                    runner.run(shards[:n_tr], n_steps, controller='bb', stats_out=stats_h[:n_tr], traces_out=tr_h)
+                    torch.cuda.synchronize()
+                tr_pass()
+                barrier()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+                tr_pass()
+                t1.record()
+                barrier()
+                ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+                e2e['traces'] = {'value': world * ep_tr * n_min / (float(ms.item()) * 1e-3), 'unit': METRIC,
+                                 'episodes_per_gpu': ep_tr, 'shards': n_tr, 'columns': ['BG', 'CGM', 'CHO', 'insulin'],
+                                 'h2d_bytes': int(sum(v.numel() * v.element_size() for sh in shards[:n_tr] for v in sh.values())),
+                                 'd2h_bytes': int(sum(t.numel() * 8 for t in tr_h) + sum(t.numel() * 8 for t in stats_h[:n_tr])),
+                                 'what': 'ShardRunner.run(traces_out=...): host inputs in, per-episode statistics AND the '
+                                         'trajectories (one row per env-step) out, device -> host copy overlapped with the '
+                                         'next shard; bounded to the first %d shards' % n_tr,
+                                 'bg_check': float(tr_h[0][-1, 0].mean())}
+                del tr_h
+            except Exception as ex:                          # noqa: BLE001  (pinned host memory is the usual suspect)
+                e2e['traces'] = {'error': repr(ex)}
         runner.close()
         del shards, stats_h
 

@@ -222,16 +222,16 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
             // own parameter row
             a_basal = (ctrl[3] > 0.0) ? ctrl[3] : c(H_BASAL);
             if (info_meal > 0.0) {
-                const double corr = sgm::div_ieee((obs > 150.0 ? 1.0 : 0.0) * (obs - ctrl[0]), ctrl[2]);
-                a_bolus = sgm::div_ieee(info_meal * st, ctrl[1]) + corr;
+                const double corr = sgm::div_cold((obs > 150.0 ? 1.0 : 0.0) * (obs - ctrl[0]), ctrl[2]);
+                a_bolus = sgm::div_cold(info_meal * st, ctrl[1]) + corr;
             } else {
                 a_bolus = 0.0;
             }
-            a_bolus = sgm::div_ieee(a_bolus, st);
+            a_bolus = sgm::div_cold(a_bolus, st);
         } else if (a.controller == 2) {                // PIDController.policy
             const double pid_integ = sd[(int64_t)SD_PID_INTEG * a.cap];
             const double pid_prev = sd[(int64_t)SD_PID_PREV * a.cap];
-            a_basal = ctrl[0] * (obs - ctrl[3]) + ctrl[1] * pid_integ + sgm::div_ieee(ctrl[2] * (obs - pid_prev), st);
+            a_basal = ctrl[0] * (obs - ctrl[3]) + ctrl[1] * pid_integ + sgm::div_cold(ctrl[2] * (obs - pid_prev), st);
             sd[(int64_t)SD_PID_PREV * a.cap] = obs;
             sd[(int64_t)SD_PID_INTEG * a.cap] = pid_integ + (obs - ctrl[3]) * st;
             a_bolus = 0.0;
@@ -255,7 +255,7 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
         }
         }
         bool aside = false;                            // RUN_CAPPED: this lane's minute was put aside
-        const double ins_kg = sgm::div_ieee(ins * 6000.0, c(H_BW));  // t1dpatient.py:122, constant over the env-step
+        const double ins_kg = sgm::div_cold(ins * 6000.0, c(H_BW));  // t1dpatient.py:122, constant over the env-step
         const double ins_mean = sgm::div_r(ins, st, r_st);
         for (int j = 0; j < st_i; j++) {               // mini_step, env.py:48-64
             int mode = MINUTE_FRESH;

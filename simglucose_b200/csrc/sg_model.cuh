@@ -112,7 +112,7 @@ __device__ __forceinline__ void stage_params(const ColT &c, Load p)
     c.set(H_rBW, sgm::rcp_nr(p(P_BW))); c.set(H_rVi, sgm::rcp_nr(p(P_Vi)));
     c.set(H_rVg, sgm::rcp_nr(p(P_Vg))); c.set(H_Dbar, 0.0); c.set(H_RPREV, 0.0);
     c.set(H_L4, sgm::log_pos(1.0e-4));
-    c.set(H_BASAL, sgm::div_ieee(p(P_u2ss) * p(P_BW), 6000.0));
+    c.set(H_BASAL, sgm::div_cold(p(P_u2ss) * p(P_BW), 6000.0));
 }
 
 // Inputs of the ODE that are constant over one simulated minute (t1dpatient.py:110:
@@ -139,8 +139,8 @@ __device__ __forceinline__ Minute minute_setup_rate(const Column<BLOCK> &c, doub
     // (same inputs, same results -- the cache cannot change a bit)
     if (m.fed && Dbar != c(H_Dbar)) {                       // t1dpatient.py:136-140
         c.set(H_Dbar, Dbar);
-        c.set(H_aa, sgm::div_ieee(sgm::div_ieee(5.0 / 2.0, 1.0 - c(H_b)), Dbar));
-        c.set(H_cc, sgm::div_ieee(sgm::div_ieee(5.0 / 2.0, c(H_d)), Dbar));
+        c.set(H_aa, sgm::div_cold(sgm::div_cold(5.0 / 2.0, 1.0 - c(H_b)), Dbar));
+        c.set(H_cc, sgm::div_cold(sgm::div_cold(5.0 / 2.0, c(H_d)), Dbar));
         c.set(H_bD, c(H_b) * Dbar);
         c.set(H_dD, c(H_d) * Dbar);
     }
@@ -252,8 +252,8 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
 __device__ __forceinline__ double pump_quantise(double amount, double vmin, double vmax, double inc)
 {
     double v = amount * 6000.0;
-    v = rint(sgm::div_ieee(v, inc)) * inc;
-    v = sgm::div_ieee(v, 6000.0);
+    v = rint(sgm::div_cold(v, inc)) * inc;
+    v = sgm::div_cold(v, 6000.0);
     v = (vmax < v) ? vmax : v;     // Python min(v, vmax)
     v = (vmin > v) ? vmin : v;     // Python max(v, vmin)
     return v;
