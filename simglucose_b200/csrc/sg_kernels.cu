@@ -162,7 +162,7 @@ __device__ __forceinline__ void episode_steps(const EpisodeArgs &a, const int64_
     int32_t *si = a.si + e;
     double x[NX];
 #pragma unroll
-    for (int i = 0; i < NX; i++) x[i] = sd[(int64_t)(SD_X0 + i) * a.cap];
+    for (int i = 0; i < NX; i++) x[i] = canonical_zero(sd[(int64_t)(SD_X0 + i) * a.cap]);
     Meal meal;
     meal.planned = sd[(int64_t)SD_PLANNED * a.cap];
     meal.last_cho = sd[(int64_t)SD_LAST_CHO * a.cap];
@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(BLOCK) patient_step_kernel(const PatientArgs p
     int32_t *si = a.si + e;
     double x[NX];
 #pragma unroll
-    for (int i = 0; i < NX; i++) x[i] = sd[(int64_t)(SD_X0 + i) * a.cap];
+    for (int i = 0; i < NX; i++) x[i] = canonical_zero(sd[(int64_t)(SD_X0 + i) * a.cap]);
     Meal meal;
     meal.planned = sd[(int64_t)SD_PLANNED * a.cap];
     meal.last_cho = sd[(int64_t)SD_LAST_CHO * a.cap];
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(BLOCK) model_kernel(const ModelArgs a)
     stage_params(c, p);
     double x[NX], dx[NX];
 #pragma unroll
-    for (int i = 0; i < NX; i++) x[i] = a.x[(int64_t)i * a.n + e];
+    for (int i = 0; i < NX; i++) x[i] = canonical_zero(a.x[(int64_t)i * a.n + e]);
     const Minute m = minute_setup(c, a.cho[e], a.insulin[e], a.last_qsto[e], a.last_food[e]);
     rhs(c, m, x, dx);
 #pragma unroll

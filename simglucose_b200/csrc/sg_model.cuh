@@ -169,11 +169,19 @@ __device__ __forceinline__ Minute minute_setup(const Column<BLOCK> &c, double ch
     return m;
 }
 
+// States enter the kernels through canonical_zero: x + 0.0 turns a -0.0 (which only a caller can supply) into +0.0 and
+// changes no other value.  From then on no state can BE -0.0 -- every trial and accepted state is a sum y + h * (..), and
+// a sum is -0.0 only if both terms are -- so "x < 0" is the sign bit, one integer test of the high word per mask
+// instead of a 64-bit compare.  ((x >= 0) * dxdt of the reference treats -0.0 like +0.0 as well.)
+__device__ __forceinline__ double canonical_zero(double x) { return x + 0.0; }
+
 __device__ __forceinline__ double mask_nonneg(double x, double dx)
 {
     // (x >= 0) * dxdt, t1dpatient.py:167,173,179,191,195,198,202 (the sign of a zero result is
     // not preserved; it never reaches an output)
-#if SG_INT_SIGN
+#if SG_INT_SIGN == 2
+    return __double2hiint(x) < 0 ? 0.0 : dx;
+#elif SG_INT_SIGN
     return sgm::is_neg(x) ? 0.0 : dx;
 #else
     return x >= 0.0 ? dx : 0.0;
@@ -211,8 +219,15 @@ __device__ __forceinline__ void rhs(const Column<BLOCK> &c, const Minute &m, con
     const double2 ke = c.pair(H_ke2);                                       // ke2, ke1
 #if SG_INT_SIGN
     const double over = x[3] - ke.x;                                        // x3 > ke2 <=> x3 - ke2 > 0 (exact in IEEE)
+#if SG_INT_SIGN == 2
+    // x3 is never -0.0, so neither is the difference: over >= +0 exactly when the sign bit is clear, and ke1 * (+0) is the
+    // 0 of the else branch
+    const double Et = __double2hiint(over) < 0 ? 0.0 : ke.y * over;        // :158-161
+#else
     const double Et = sgm::is_pos(over) ? ke.y * over : 0.0;                // :158-161
-    const double egp = sgm::is_neg(EGPt) ? 0.0 : EGPt;                      // max(EGPt, 0) :165
+#endif
+    // (EGPt = kp1 - .. - .. is -0.0 only if kp1 is: the sign bit decides here too; max(-0.0, 0) and 0.0 are equal)
+    const double egp = (SG_INT_SIGN >= 2 ? __double2hiint(EGPt) < 0 : sgm::is_neg(EGPt)) ? 0.0 : EGPt;   // max(EGPt, 0) :165
 #else
     const double Et = (x[3] > ke.x) ? ke.y * (x[3] - ke.x) : 0.0;           // :158-161
     const double egp = (0.0 > EGPt) ? 0.0 : EGPt;                           // max(EGPt, 0) :165

@@ -245,6 +245,38 @@ def test_custom_reward_function():
     assert len(seen[0]) == 2 and max(len(s) for s in seen) == 20       # int(60 / 3) samples, env.py:100-102
 
 
+def test_model_masks_at_signed_zeros_and_negative_states():
+    """(x >= 0) * dxdt (t1dpatient.py:167-202): -0.0 counts as non-negative in the reference, negative states freeze
+    their derivative.  The kernels test the sign BIT of the state after turning a caller's -0.0 into +0.0 at entry
+    (csrc/sg_model.cuh canonical_zero): T1DPatient.model against the oracle for zero, -0.0, tiny and negative entries in
+    the seven masked states, and max(EGPt, 0) / the renal threshold on either side."""
+    from simglucose_b200.patient.t1dpatient import Action, T1DPatient
+    p = T1DPatient.withID(7)
+    prm, x0 = O.patient_params(6)
+    masked = [3, 4, 5, 9, 10, 11, 12]
+    cases = []
+    for v in (0.0, -0.0, 5e-324, -5e-324, -1e-300, -3.5e-12, -1.0, 2.2250738585072014e-308):
+        x = x0.copy()
+        x[masked] = v
+        cases.append(x)
+    for k in masked:
+        x = x0.copy()
+        x[k] = -0.0
+        cases.append(x)
+        x = x0.copy()
+        x[k] = -x[k] - 1.0
+        cases.append(x)
+    hi = x0.copy(); hi[3] = 5000.0; hi[8] = 900.0          # EGPt < 0 and x3 above the renal threshold ke2 = 339
+    at = x0.copy(); at[3] = float(p._params['ke2'])        # exactly at the threshold: Et = 0
+    cases += [hi, at]
+    for x in cases:
+        for cho, lq, lf in ((0.0, 0.0, 0.0), (5.0, 120.0, 35.0)):
+            dx = T1DPatient.model(0.0, x, Action(CHO=cho, insulin=0.02), p._params, lq, lf)
+            ref = O.model(x, cho, 0.02, prm, lq, lf)
+            assert np.array_equal(np.asarray(dx)[masked] == 0.0, np.asarray(ref)[masked] == 0.0), (x, dx, ref)
+            assert H.rel_err(dx, ref) <= 1e-12, (x, dx, ref)
+
+
 def test_patient_step_and_model_against_oracle():
     """T1DPatient.step / .model (t1dpatient.py:82-208) minute by minute, with a meal and a bolus."""
     from simglucose_b200.patient.t1dpatient import Action, T1DPatient
