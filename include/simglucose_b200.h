@@ -161,6 +161,17 @@ int sg_set_step_cap(sg_handle h, int32_t cap);
  * sg_run is cut into one launch per segment (plus three small sort launches); sg_step re-sorts every segment_steps calls.
  * The scratch (8 B per episode of capacity + the histogram) is allocated here.  segment_steps * sample_time <= 4096. */
 int sg_set_coherence(sg_handle h, int32_t segment_steps);
+
+/* What the launch order of sg_set_coherence is sorted by.
+ *   0 (default)  the next meal event, as described above: for orders that are kept for tens of env-steps;
+ *   1            adaptive, for orders that are re-sorted every few env-steps (a lockstep vector environment whose
+ *                environments restart one by one): an episode with a meal announced inside the segment is keyed by
+ *                (minutes until it, grams); every other episode by the DOPRI5 steps per env-step it took since the
+ *                previous sort (statistics row SG_STAT dopri_steps), restarted episodes last -- a fresh start costs
+ *                8 - 9 steps in its first minute and 4 - 5 for the next twenty against 3 for a settled episode, and
+ *                whatever else makes an episode expensive shows in the steps it just took.
+ * Like the order itself this cannot reach a result.  8 B of scratch per episode of capacity for mode 1. */
+int sg_set_sort_mode(sg_handle h, int32_t mode);
 /* The current launch order perm_out [E] (a permutation of 0..E-1); SG_ERR_STATE before the first sorted launch. */
 int sg_get_launch_order(sg_handle h, int32_t *perm_out, void *stream);
 

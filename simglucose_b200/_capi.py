@@ -32,7 +32,7 @@ STATUS_STREAM_EXHAUSTED = -5
 SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_hardware', 'sg_load_params',
            'sg_reset', 'sg_step', 'sg_run', 'sg_get_state', 'sg_get_stats', 'sg_get_status',
            'sg_reduce_stats', 'sg_num_episodes', 'sg_launch_count',
-           'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_set_step_cap', 'sg_set_coherence', 'sg_get_launch_order',
+           'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_set_step_cap', 'sg_set_coherence', 'sg_set_sort_mode', 'sg_get_launch_order',
            'sg_reset_masked', 'sg_patient_step', 'sg_model', 'sg_pump',
            'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
            'sg_report_stats', 'sg_cvga_zones',
@@ -77,6 +77,7 @@ def load():
     L.sg_set_t0.argtypes = [vp, C.c_int32]
     L.sg_set_step_cap.argtypes = [vp, C.c_int32]
     L.sg_set_coherence.argtypes = [vp, C.c_int32]
+    L.sg_set_sort_mode.argtypes = [vp, C.c_int32]
     L.sg_get_launch_order.argtypes = [vp, ip, vp]
     L.sg_reset_masked.argtypes = [vp, ip, dp, dp, vp]
     L.sg_patient_step.argtypes = [vp, dp, dp, dp, vp]

@@ -64,6 +64,8 @@ struct sg_context {
     bool perm_valid = false;
     int32_t *perm = nullptr, *sort_keys = nullptr, *sort_hist = nullptr;
     int32_t sort_n_keys = 0;
+    int32_t sort_mode = 0;             // sg_set_sort_mode: 0 by next meal event, 1 adaptive (recent DOPRI5 steps)
+    double *sort_prev_steps = nullptr;
     // episodes with positions of their own (sg_reset_masked): the host-side stream length check no longer applies
     bool per_episode_positions = false;
     int64_t steps_total = 0;           // env-steps launched since sg_create (Philox counter of SG_CTRL_RANDOM)
@@ -145,7 +147,7 @@ int sg_destroy(sg_handle h)
     cudaFree(h->sd); cudaFree(h->si); cudaFree(h->stats); cudaFree(h->partials);
     cudaFree(h->table); cudaFree(h->table_x0);
     cudaFree(h->defer_d); cudaFree(h->defer_i); cudaFree(h->defer_list); cudaFree(h->defer_count);
-    cudaFree(h->perm); cudaFree(h->sort_keys); cudaFree(h->sort_hist);
+    cudaFree(h->perm); cudaFree(h->sort_keys); cudaFree(h->sort_hist); cudaFree(h->sort_prev_steps);
     delete h;
     return SG_OK;
 }
@@ -215,8 +217,9 @@ static int sort_episodes(sg_handle h, cudaStream_t stream)
     sa.n = h->n; sa.cap = h->cap; sa.sd = h->sd; sa.si = h->si;
     sa.meal_minute = h->meal_minute; sa.meal_grams = h->meal_grams; sa.max_meals = h->max_meals;
     sa.patient_row = h->patient_row;
-    static const int sort_mode = getenv("SG_SORT_MODE") ? atoi(getenv("SG_SORT_MODE")) : 0;    // experiment knob
-    sa.mode = sort_mode;
+    sa.mode = h->sort_mode == 1 ? 2 : 0;
+    sa.stats = h->stats; sa.prev_steps = h->sort_prev_steps;
+    sa.steps_between = h->coherence_steps; sa.st = h->hw.st;
     sa.window = h->coherence_steps * h->hw.st;
     sa.n_keys = h->sort_n_keys;
     sa.keys = h->sort_keys; sa.hist = h->sort_hist; sa.perm = h->perm;
@@ -370,6 +373,20 @@ int sg_set_coherence(sg_handle h, int32_t segment_steps)
         h->sort_n_keys = n_keys;
     }
     h->coherence_steps = segment_steps;
+    h->perm_valid = false;
+    return SG_OK;
+}
+
+int sg_set_sort_mode(sg_handle h, int32_t mode)
+{
+    if (!h || mode < 0 || mode > 1) return fail(SG_ERR_ARG, "sg_set_sort_mode: mode 0 (next meal event) or 1 (adaptive)");
+    DeviceGuard g(h->device);
+    if (mode == 1 && !h->sort_prev_steps) {
+        cudaError_t ce = cudaMalloc(&h->sort_prev_steps, sizeof(double) * h->cap);
+        if (ce == cudaSuccess) ce = cudaMemset(h->sort_prev_steps, 0, sizeof(double) * h->cap);
+        if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_sort_mode: cudaMalloc", ce);
+    }
+    h->sort_mode = mode;
     h->perm_valid = false;
     return SG_OK;
 }

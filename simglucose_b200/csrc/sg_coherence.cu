@@ -31,7 +31,33 @@ __global__ void __launch_bounds__(SBLOCK) key_hist_kernel(const SortArgs a)
     int pos = a.si[(int64_t)SI_MEAL_POS * a.cap + e];
     const double planned = a.sd[(int64_t)SD_PLANNED * a.cap + e];
     int key = a.n_keys - 1;
-    if (planned > 0.0) {
+    if (a.mode == 2) {
+        // Adaptive key, for launch orders that are re-sorted every few env-steps (lockstep vector environments):
+        //   [0, 64)                      DOPRI5 steps per env-step since the previous sort above the calm level of
+        //                                3 per minute; 63 = an episode that was (re)started since then -- its first
+        //                                minute costs 8 - 9 steps and the next twenty 4 - 5 (states that are exactly
+        //                                zero are held to atol = 1e-12 until they have grown)
+        //   64 + dt * 128 + grams        a meal announced in dt < window minutes (the onset minute costs up to 36)
+        // Whatever makes an episode expensive -- a fresh start, eating, the hour after a meal, a jump of the insulin
+        // rate -- shows in the steps it just took, and such episodes end up in the same warps.
+        const double cum = a.stats[(int64_t)14 * a.cap + e];
+        const double prev = a.prev_steps[e];
+        a.prev_steps[e] = cum;
+        const double per_step = (cum - prev) / (double)(a.steps_between > 0 ? a.steps_between : 1);
+        int b = (cum < prev || cum == 0.0) ? 63 : (int)(per_step + 0.5) - 3 * a.st;
+        key = b < 0 ? 0 : (b > 63 ? 63 : b);
+        int mm = -1;
+        while (pos < a.max_meals) {
+            mm = a.meal_minute[(int64_t)pos * a.n + e];
+            if (mm < 0 || mm >= minute) break;
+            pos++;
+        }
+        if (planned <= 0.0 && pos < a.max_meals && mm >= minute && mm - minute < a.window) {
+            int g = (int)a.meal_grams[(int64_t)pos * a.n + e];
+            g = g < 0 ? 0 : (g > GRAM_BUCKETS - 1 ? GRAM_BUCKETS - 1 : g);
+            key = 64 + (mm - minute) * GRAM_BUCKETS + g;
+        }
+    } else if (planned > 0.0) {
         const int left = (int)ceil(planned / 5.0);                    // EAT_RATE, t1dpatient.py:20
         key = left < GRAM_BUCKETS - 1 ? left : GRAM_BUCKETS - 1;
     } else {
@@ -44,7 +70,6 @@ __global__ void __launch_bounds__(SBLOCK) key_hist_kernel(const SortArgs a)
         if (pos < a.max_meals && mm >= minute && mm - minute < a.window) {
             int g = (int)a.meal_grams[(int64_t)pos * a.n + e];
             g = g < 0 ? 0 : (g > GRAM_BUCKETS - 1 ? GRAM_BUCKETS - 1 : g);
-            if (a.mode == 1 && a.patient_row) g = (a.patient_row[e] & 31) * 4 + (g >> 5);   // same patient first
             key = (mm - minute + 1) * GRAM_BUCKETS + g;
         }
     }

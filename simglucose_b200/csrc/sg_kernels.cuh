@@ -165,7 +165,13 @@ struct SortArgs {
     const double *meal_grams;
     int32_t max_meals;
     const int32_t *patient_row;    // [n] or null
-    int32_t mode;                  // 0: key (minute, grams); 1: key (minute, patient row, grams / 8)
+    int32_t mode;                  // 0: key (minute, grams); 1: key (minute, patient row, grams / 8); 2: adaptive
+    // mode 2 (sg_set_sort_mode(h, 1)): episodes without a meal onset inside the window are keyed by the DOPRI5 steps
+    // they took since the previous sort (statistics row 14; prev_steps keeps the last value seen per episode)
+    const double *stats;           // [NSTAT][cap]
+    double *prev_steps;            // [cap]
+    int32_t steps_between;         // env-steps between two sorts (normalises the step count)
+    int32_t st;                    // sample_time
     int32_t window;                // minutes ahead that are told apart (the segment until the next sort)
     int32_t n_keys;                // key_count(window)
     int32_t *keys;                 // [cap] scratch

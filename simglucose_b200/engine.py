@@ -156,12 +156,17 @@ class BatchEngine:
         _capi.check(self.lib.sg_set_step_cap(self._h, int(cap)))
         self.step_cap = int(cap)
 
-    def set_coherence(self, segment_steps):
+    def set_coherence(self, segment_steps, adaptive=False):
         """Schedule-coherent launch order (sg_set_coherence): every `segment_steps` env-steps the episodes are sorted
         by the minute of their next meal event, so that the lanes of a warp meet the expensive minutes together.
-        For populations whose episodes have meal schedules of their own; per-episode results do not change.  0 = off."""
+        For populations whose episodes have meal schedules of their own; per-episode results do not change.  0 = off.
+        adaptive (sg_set_sort_mode 1): sort by the DOPRI5 steps every episode took since the previous sort and by the
+        meals announced inside the segment -- for orders that are re-sorted every few env-steps (lockstep stepping of
+        environments that restart one by one)."""
         _capi.check(self.lib.sg_set_coherence(self._h, int(segment_steps)))
+        _capi.check(self.lib.sg_set_sort_mode(self._h, 1 if adaptive else 0))
         self.coherence = int(segment_steps)
+        self.adaptive_sort = bool(adaptive)
 
     def launch_order(self):
         """The current sorted launch order [E] int32 (thread i owns episode perm[i])."""

@@ -43,7 +43,7 @@ class T1DSimVecEnv(object):
     def __init__(self, num_envs, patient_names=None, seed=0, start_hour=0, horizon_steps=480, sensor='Dexcom',
                  pump='Insulet', stream_mode='device', group_size=1, params=None, x0=None, auto_reset=False,
                  device=0, carry_h=False, fma=False, episode_offset=0, step_cap=None, reward_fun=None, fp32=False,
-                 gym_seeding=False, coherence=None):
+                 gym_seeding=False, coherence=None, adaptive_sort=None):
         """patient_names: list of names / 1-based ids cycled over the environments (default: the 30 virtual
         patients in table order).  params [32, E] / x0 [13, E]: per-environment overrides (perturbed
         populations; x0 is ignored with gym_seeding, which randomises the table state).  group_size: environments
@@ -72,7 +72,9 @@ class T1DSimVecEnv(object):
         self.engine.set_step_cap(self.step_cap)
         auto = 40 if (own_schedules and self.num_envs >= 65536 and not self.step_cap) else 0
         self.coherence = auto if coherence is None else int(coherence)
-        self.engine.set_coherence(self.coherence)
+        # environments that restart one by one: re-sort often, by what every episode just cost (BatchEngine.set_coherence)
+        self.adaptive_sort = bool(adaptive_sort) if adaptive_sort is not None else False
+        self.engine.set_coherence(self.coherence, adaptive=self.adaptive_sort)
         names = P.patient_names() if patient_names is None else list(patient_names)
         rows = np.array([P.patient_row(n) for n in names], dtype=np.int32)
         self._rows_host = rows[np.arange(self.num_envs) % len(rows)]

@@ -25,4 +25,4 @@ for f in ('bench_config3_${N}gpu','bench_${N}gpu'):
         print('  vector', d['population_vector_hex'])
     except Exception as e: print(f, 'failed', e)
 PY
-tail -5 $OUT/*.err
+for f in $OUT/*.err; do tail -n 3 $f; done

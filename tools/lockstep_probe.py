@@ -24,10 +24,16 @@ def timed(fn):
 
 
 for mode in modes:
+    # 'gym@4a': the gym environment with the launch order re-sorted every 4 env-steps in adaptive mode ('gym@40': by meals)
+    mode, _, sort = mode.partition('@')
     gym = mode == 'gym'
-    env = T1DSimVecEnv(E, seed=0, horizon_steps=480, gym_seeding=gym, auto_reset=gym)
+    kw = {}
+    if sort:
+        kw = dict(coherence=int(sort.rstrip('a')), adaptive_sort=sort.endswith('a'))
+    env = T1DSimVecEnv(E, seed=0, horizon_steps=480, gym_seeding=gym, auto_reset=gym, **kw)
+    mode = mode + ('@' + sort if sort else '')
     env.reset()
-    for _ in range(45):                                   # past the first sort and the first resets
+    for _ in range(125):                                  # past the first sorts and into the steady state of the resets
         env.step_random(0.0, 0.05)
     if mode == 'kernel':
         def loop():
