@@ -79,6 +79,9 @@ def parse():
                     help='env-steps between two sorts of the launch order (sg_set_coherence); -1 = the default of the '
                          'workload (40 for resident populations; 0 for the one-wave shards of the e2e leg, where every '
                          'launch boundary costs a tail)')
+    ap.add_argument('--adaptive-sort', action='store_true',
+                    help='sort the launch order by the DOPRI5 steps every episode just took (sg_set_sort_mode 1) instead of '
+                         'by its next meal event')
     ap.add_argument('--cpu-seconds', type=float, default=15.0, help='target duration of the cpu_baseline sample')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
@@ -401,7 +404,7 @@ def config2(local, envs=1048576, n_steps=480, fp32=False, coherence=None, auto_r
             'population_current_episodes': agg}
 
 
-def config3(local, rank, world, total, days, wave, coherence, seed=1234, carry_h=False, fma=False):
+def config3(local, rank, world, total, days, wave, coherence, seed=1234, carry_h=False, fma=False, adaptive=False):
     """configs[3]: `total` episodes with +-10 % perturbed parameters x `days`, BBController (nominal basal by name),
     independent scenario / sensor streams per episode, sharded over the ranks in contiguous ranges and simulated in
     resident waves; parameters and streams are generated on device per wave, keyed by GLOBAL episode index, so the
@@ -416,7 +419,7 @@ def config3(local, rank, world, total, days, wave, coherence, seed=1234, carry_h
     lo, hi = shard_range(total, rank, world)
     n_steps = days * 480
     cap = min(wave, hi - lo)
-    eng = BatchEngine(cap, device=local, coherence=coherence, carry_h=carry_h, fma=fma)
+    eng = BatchEngine(cap, device=local, coherence=coherence, carry_h=carry_h, fma=fma, adaptive_sort=adaptive)
     noise_buf = torch.empty((n_steps + 2) * cap, dtype=torch.float64, device=dev)
     agg = torch.zeros(_capi.NSTAT, dtype=torch.float64, device=dev)
     agg[2], agg[3] = float('inf'), float('-inf')
@@ -592,7 +595,8 @@ def main():
     # inputs resident in HBM before the timed region
     noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=1, episode_offset=ep0, group_size=30, device=dev)
     mm, mg = S.device_scenarios(E, n_min, start_minute=0, seed=1, episode_offset=ep0, group_size=30, device=dev)
-    eng = BatchEngine(E, device=local, carry_h=args.carry_h, fma=args.fma, fp32=args.fp32, coherence=coherence)
+    eng = BatchEngine(E, device=local, carry_h=args.carry_h, fma=args.fma, fp32=args.fp32, coherence=coherence,
+                      adaptive_sort=args.adaptive_sort)
     agg = torch.zeros(_capi.NSTAT, dtype=torch.float64, device=dev)
     agg_all = torch.zeros(_capi.NSTAT, dtype=torch.float64, device=dev)
 

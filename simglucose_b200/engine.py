@@ -29,8 +29,9 @@ class BatchEngine:
     """
 
     def __init__(self, capacity, device=0, carry_h=False, fma=False, sensor='Dexcom', pump='Insulet', fp32=False,
-                 coherence=0):
-        """coherence: env-steps between two sorts of the launch order (set_coherence); 0 = off."""
+                 coherence=0, adaptive_sort=False):
+        """coherence: env-steps between two sorts of the launch order (set_coherence); 0 = off.  adaptive_sort: sort by
+        what every episode just cost instead of by its next meal event (set_coherence)."""
         if not torch.cuda.is_available():
             raise _capi.SgError('simglucose_b200 needs a CUDA device (there is no CPU fallback)')
         self.lib = _capi.load()
@@ -48,8 +49,9 @@ class BatchEngine:
         self.load_table(tbl, x0)
         self.step_cap = 0
         self.coherence = 0
+        self.adaptive_sort = False
         if coherence:
-            self.set_coherence(coherence)
+            self.set_coherence(coherence, adaptive=adaptive_sort)
 
     # -- configuration ---------------------------------------------------------------------------
     def set_hardware(self, sensor='Dexcom', pump='Insulet'):

@@ -76,6 +76,16 @@ def test_coherent_launch_order_is_bit_identical(controller, fp32):
         assert l1 == 1 + n_seg * 4 and l0 == 2             # reset + (3 sort launches + 1 episode launch) per segment
     heavy = int((base['counters'][:, 0, :] > 5).sum())
     assert heavy > 100                                     # there were expensive minutes to line up
+    # the adaptive order (sg_set_sort_mode 1: recent DOPRI5 steps + meals announced inside the segment), re-sorted every
+    # few env-steps as a lockstep vector environment does: the same results, a permutation, expensive episodes together
+    eng = BatchEngine(E, fp32=fp32)
+    eng.set_coherence(4, adaptive=True)
+    eng.reset(rows, noise, mm, mg, row0=False)
+    out = eng.run(n_steps, controller=controller, trace=True, counters=True, **kw)
+    _same(base, _snapshot(eng, out))
+    perm = eng.launch_order().cpu().numpy()
+    assert np.array_equal(np.sort(perm), np.arange(E))
+    eng.close()
 
 
 def test_coherent_order_groups_meal_onsets():

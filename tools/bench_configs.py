@@ -29,12 +29,12 @@ from simglucose_b200 import _capi  # noqa: E402
 from simglucose_b200.distributed import summarize  # noqa: E402
 
 
-def c3(scale, coherence):
+def c3(scale, coherence, adaptive=False):
     n = int(2097152 * scale) // 64 * 64
-    bench.config3(0, 0, 1, max(65536, n // 32), 1, n, coherence)                       # warm-up
-    sec, agg, failed, launches, gen_s, _ = bench.config3(0, 0, 1, n, 7, n, coherence)
+    bench.config3(0, 0, 1, max(65536, n // 32), 1, n, coherence, adaptive=adaptive)                       # warm-up
+    sec, agg, failed, launches, gen_s, _ = bench.config3(0, 0, 1, n, 7, n, coherence, adaptive=adaptive)
     return {'config': 'configs[3] one resident wave: %d episodes with +-10 %% perturbed parameters x 7 days, BBController, '
-                      'independent streams, coherence_steps %d' % (n, coherence),
+                      'independent streams, coherence_steps %d%s' % (n, coherence, ' (adaptive sort)' if adaptive else ''),
             'value': n * 10080 / sec, 'unit': bench.METRIC, 'seconds': sec, 'stream_generation_s': gen_s,
             'library_launches': launches, 'solver_failures': failed, 'population': summarize(agg),
             'population_vector_hex': bench.vector_hex(agg)}
@@ -56,6 +56,7 @@ def main():
         '2f': lambda: bench.config2(0, envs=int(1048576 * sc), n_steps=480, fp32=True),
         '3': lambda: c3(sc, 40),
         '3plain': lambda: c3(sc, 0),
+        '3a10': lambda: c3(sc, 10, True), '3a20': lambda: c3(sc, 20, True), '3a40': lambda: c3(sc, 40, True),
         '4': lambda: bench.config4(0, seeds=int(10000 * sc)),
     }
     for name in args.only.split(','):
