@@ -28,7 +28,7 @@ CTRL = {'actions': 0, 'bb': 1, 'pid': 2}
 class Config(C.Structure):
     _fields_ = [('sample_time', C.c_int), ('sensor_min', C.c_double), ('sensor_max', C.c_double),
                 ('pump', C.c_double * 6), ('controller', C.c_int), ('ctrl', C.c_double * 6),
-                ('carry_h', C.c_int)]
+                ('carry_h', C.c_int), ('t0', C.c_int)]
 
 
 def build():
@@ -122,7 +122,7 @@ def _ip(a):
 
 
 def make_config(controller='bb', ctrl=(140.0, 1.0, 1.0), sensor_name='Dexcom', pump_name='Insulet',
-                carry_h=0):
+                carry_h=0, t0=0):
     s, pm = sensor(sensor_name), pump(pump_name)
     cfg = Config()
     cfg.sample_time = int(s['sample_time'])
@@ -133,6 +133,7 @@ def make_config(controller='bb', ctrl=(140.0, 1.0, 1.0), sensor_name='Dexcom', p
     c = list(ctrl) + [0.0] * (6 - len(ctrl))
     cfg.ctrl[:] = c
     cfg.carry_h = int(carry_h)
+    cfg.t0 = int(t0)
     return cfg
 
 
@@ -156,9 +157,10 @@ def risk(bg):
 
 def run_episode(params, x0, n_steps, meal_minute, meal_grams, noise, controller='bb',
                 ctrl=(140.0, 1.0, 1.0), actions=None, sensor_name='Dexcom', pump_name='Insulet',
-                carry_h=0):
-    """One closed-loop episode; returns dict(trace columns..., counters, stats, final_state, status)."""
-    cfg = make_config(controller, ctrl, sensor_name, pump_name, carry_h)
+                carry_h=0, t0=0):
+    """One closed-loop episode; returns dict(trace columns..., counters, stats, final_state, status).
+    t0: T1DPatient(t0=...); meal_minute counts from scenario.start_time."""
+    cfg = make_config(controller, ctrl, sensor_name, pump_name, carry_h, t0)
     st = cfg.sample_time
     p = np.ascontiguousarray(params, dtype=np.float64)
     x0 = np.ascontiguousarray(x0, dtype=np.float64)

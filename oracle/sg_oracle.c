@@ -328,7 +328,7 @@ int sgo_run_episode(const sgo_config *cfg, const double *p, const double *x0, in
 
     /* patient.reset(), t1dpatient.py:247-281 (x0 is the post-reset init_state) */
     memcpy(s.x, x0, sizeof s.x);
-    s.t = 0.0;
+    s.t = (double)cfg->t0;     /* t1dpatient.py:277: self._odesolver.set_initial_value(self.init_state, self.t0) */
     s.planned_meal = 0.0; s.last_cho = 0.0;
     s.last_Qsto = x0[0] + x0[1]; s.last_foodtaken = 0.0; s.is_eating = 0;
     s.h_carry = 0.0; s.last_cgm = 0.0; s.noise_pos = 0;
@@ -401,9 +401,11 @@ int sgo_run_episode(const sgo_config *cfg, const double *p, const double *x0, in
         for (int j = 0; j < st_i; j++) {
             /* mini_step, env.py:48-64; scenario.get_action(self.time) with time = start + patient.t */
             int minute = k * st_i + j;
+            /* env.time = scenario.start_time + patient.t minutes (env.py:44-46): the table is in minutes after start_time */
+            const int clock = cfg->t0 + minute;
             double meal = 0.0;
-            while (mpos < n_meals && meal_minute[mpos] >= 0 && meal_minute[mpos] < minute) mpos++;
-            if (mpos < n_meals && meal_minute[mpos] == minute) meal = meal_grams[mpos];
+            while (mpos < n_meals && meal_minute[mpos] >= 0 && meal_minute[mpos] < clock) mpos++;
+            if (mpos < n_meals && meal_minute[mpos] == clock) meal = meal_grams[mpos];
             double basal = sgo_pump(a_basal, cfg->pump[0], cfg->pump[1], cfg->pump[2]);
             double bolus = sgo_pump(a_bolus, cfg->pump[3], cfg->pump[4], cfg->pump[5]);
             double ins = basal + bolus;

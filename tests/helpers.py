@@ -53,4 +53,5 @@ def oracle_episode(d, i, carry_h=0):
     mm, mg = d['meal_minute'][i], d['meal_grams'][i]
     k = mm >= 0
     return O.run_episode(p, d['x0'][i], int(d['n_steps'][i]), mm[k], mg[k], d['noise'][i], controller=kind,
-                         ctrl=ctrl, actions=d['actions'][i], sensor_name=sn, pump_name=pn, carry_h=carry_h)
+                         ctrl=ctrl, actions=d['actions'][i], sensor_name=sn, pump_name=pn, carry_h=carry_h,
+                         t0=int(d['t0'][i]) if 't0' in d else 0)

@@ -30,7 +30,7 @@ def _compare(d, i, o, tol=1e-9):
 
 
 @pytest.mark.parametrize('fixture', ['golden_config', 'custom_scenario', 'open_loop_actions', 'hardware_0',
-                                     'hardware_1', 'hardware_2'])
+                                     'hardware_1', 'hardware_2', 'late_start'])       # late_start: T1DPatient(t0 = 1, 2, 3, 7)
 def test_oracle_matches_reference(fixture):
     d = H.load(fixture)
     for i in range(d['patient_row'].shape[0]):
