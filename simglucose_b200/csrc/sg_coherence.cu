@@ -20,13 +20,9 @@ using namespace sgk;
 
 constexpr int SBLOCK = 256;
 
-// key of every episode + histogram (warp-aggregated atomics: most lanes of a warp share the "no meal" bucket)
-__global__ void __launch_bounds__(SBLOCK) key_hist_kernel(const SortArgs a)
+// The sort key of episode e (see the header comment and, for mode 2, the comment inside).
+__device__ __forceinline__ int episode_key(const SortArgs &a, int64_t e)
 {
-    const int64_t e = (int64_t)blockIdx.x * SBLOCK + threadIdx.x;
-    const bool valid = e < a.n;
-    const unsigned act = __ballot_sync(0xffffffffu, valid);
-    if (!valid) return;
     const int minute = a.si[(int64_t)SI_MINUTE * a.cap + e];
     int pos = a.si[(int64_t)SI_MEAL_POS * a.cap + e];
     const double planned = a.sd[(int64_t)SD_PLANNED * a.cap + e];
@@ -73,9 +69,60 @@ __global__ void __launch_bounds__(SBLOCK) key_hist_kernel(const SortArgs a)
             key = (mm - minute + 1) * GRAM_BUCKETS + g;
         }
     }
+    return key;
+}
+
+// key of every episode + histogram (warp-aggregated atomics: most lanes of a warp share the "no meal" bucket)
+__global__ void __launch_bounds__(SBLOCK) key_hist_kernel(const SortArgs a)
+{
+    const int64_t e = (int64_t)blockIdx.x * SBLOCK + threadIdx.x;
+    const bool valid = e < a.n;
+    const unsigned act = __ballot_sync(0xffffffffu, valid);
+    if (!valid) return;
+    const int key = episode_key(a, e);
     a.keys[e] = key;
     const unsigned peers = __match_any_sync(act, key);
     if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(a.hist + key, __popc(peers));
+}
+
+// The same two passes for SMALL key spaces (a launch order that is re-sorted every env-step tells only the next few
+// minutes apart: 513 keys at a 3-minute segment): the histogram of a block lives in shared memory, so an episode costs
+// a shared-memory atomic and a block a global one per key it holds -- nearly every episode of such a sort sits in the
+// same handful of "calm" buckets, which serialised the warp-aggregated global atomics of the general path.
+constexpr int SMALL_KEYS = 1024;
+
+__global__ void __launch_bounds__(SBLOCK) key_hist_small_kernel(const SortArgs a)
+{
+    __shared__ int32_t sh[SMALL_KEYS];
+    for (int i = threadIdx.x; i < a.n_keys; i += SBLOCK) sh[i] = 0;
+    __syncthreads();
+    const int64_t e = (int64_t)blockIdx.x * SBLOCK + threadIdx.x;
+    if (e < a.n) {
+        const int key = episode_key(a, e);
+        a.keys[e] = key;
+        atomicAdd(&sh[key], 1);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.n_keys; i += SBLOCK)
+        if (sh[i]) atomicAdd(a.hist + i, sh[i]);
+}
+
+__global__ void __launch_bounds__(SBLOCK) scatter_small_kernel(const SortArgs a)
+{
+    __shared__ int32_t cnt[SMALL_KEYS], base[SMALL_KEYS];
+    for (int i = threadIdx.x; i < a.n_keys; i += SBLOCK) cnt[i] = 0;
+    __syncthreads();
+    const int64_t e = (int64_t)blockIdx.x * SBLOCK + threadIdx.x;
+    int key = 0, rank = 0;
+    if (e < a.n) {
+        key = a.keys[e];
+        rank = atomicAdd(&cnt[key], 1);                  // arrival order inside the block: any order will do
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.n_keys; i += SBLOCK)
+        if (cnt[i]) base[i] = atomicAdd(a.hist + i, cnt[i]);
+    __syncthreads();
+    if (e < a.n) a.perm[base[key] + rank] = (int32_t)e;
 }
 
 // exclusive prefix sum of the histogram in place: one block, every thread owns a run of consecutive buckets
@@ -135,9 +182,12 @@ cudaError_t launch_sort(const SortArgs &a, cudaStream_t s)
     cudaError_t e = cudaMemsetAsync(a.hist, 0, sizeof(int32_t) * a.n_keys, s);
     if (e != cudaSuccess) return e;
     const unsigned blocks = (unsigned)((a.n + SBLOCK - 1) / SBLOCK);
-    key_hist_kernel<<<blocks, SBLOCK, 0, s>>>(a);
+    const bool small = a.n_keys <= SMALL_KEYS;
+    if (small) key_hist_small_kernel<<<blocks, SBLOCK, 0, s>>>(a);
+    else key_hist_kernel<<<blocks, SBLOCK, 0, s>>>(a);
     scan_kernel<<<1, 1024, 0, s>>>(a.hist, a.n_keys);
-    scatter_kernel<<<blocks, SBLOCK, 0, s>>>(a);
+    if (small) scatter_small_kernel<<<blocks, SBLOCK, 0, s>>>(a);
+    else scatter_kernel<<<blocks, SBLOCK, 0, s>>>(a);
     return cudaGetLastError();
 }
 

@@ -78,14 +78,20 @@ def test_coherent_launch_order_is_bit_identical(controller, fp32):
     assert heavy > 100                                     # there were expensive minutes to line up
     # the adaptive order (sg_set_sort_mode 1: recent DOPRI5 steps + meals announced inside the segment), re-sorted every
     # few env-steps as a lockstep vector environment does: the same results, a permutation, expensive episodes together
-    eng = BatchEngine(E, fp32=fp32)
-    eng.set_coherence(4, adaptive=True)
-    eng.reset(rows, noise, mm, mg, row0=False)
-    out = eng.run(n_steps, controller=controller, trace=True, counters=True, **kw)
-    _same(base, _snapshot(eng, out))
-    perm = eng.launch_order().cpu().numpy()
-    assert np.array_equal(np.sort(perm), np.arange(E))
-    eng.close()
+    # (segments of 1 and 2 env-steps have fewer than 1,024 keys and take the shared-memory histogram path of the sort)
+    for seg, adaptive in ((4, True), (1, True), (2, False)):
+        eng = BatchEngine(E, fp32=fp32)
+        eng.set_coherence(seg, adaptive=adaptive)
+        eng.reset(rows, noise, mm, mg, row0=False)
+        out = eng.run(n_steps if seg > 1 else 60, controller=controller, trace=True, counters=True, **kw)
+        snap = _snapshot(eng, out)
+        if seg > 1:
+            _same(base, snap)
+        else:                                              # 60 one-step segments: against the first 60 steps of the unsorted run
+            assert torch.equal(snap['trace'], base['trace'][:60]) and torch.equal(snap['counters'], base['counters'][:180])
+        perm = eng.launch_order().cpu().numpy()
+        assert np.array_equal(np.sort(perm), np.arange(E))
+        eng.close()
 
 
 def test_coherent_order_groups_meal_onsets():
