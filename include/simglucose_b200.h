@@ -273,6 +273,34 @@ int sg_get_status(sg_handle h, int32_t *status_out /* [E] */, void *stream);
  * FIRST_DONE = number of episodes that ever reported done). */
 int sg_reduce_stats(sg_handle h, double *agg_out, void *stream);
 
+/* The same aggregate for callers that may not allocate device memory.  (No counterpart in the reference: it has no
+ * device and no allocator; this exists for the hosts described next.)
+ *
+ * Who needs it: code that is handed device pointers by an embedding application but is not allowed to call
+ * cudaMalloc itself -- a plugin under a fixed memory budget, a host whose pool allocator must account for every
+ * byte, a real-time loop in which a driver allocation could block.  Such a caller cannot hold an sg_handle
+ * (sg_create allocates the resident state and the reduction's partial-sum buffer), so this entry point takes the
+ * per-episode statistics directly and keeps its partial sums in an array compiled into the library:
+ * SG_REDUCE_STATIC_MAX_BLOCKS x SG_NSTAT doubles = 75,776 bytes, held by every GPU on which the library's code is
+ * loaded until the process exits.  It calls no cudaMalloc / cudaFree and no allocating library routine.
+ *
+ *   stats     [SG_NSTAT][capacity] device, the layout sg_get_stats writes (capacity = row stride >= n_episodes)
+ *   agg_out   [SG_NSTAT] device; bit-identical to what sg_reduce_stats gives for the same statistics
+ *   limit     n_episodes <= SG_REDUCE_STATIC_MAX_EPISODES (the largest population BASELINE.json names, and the
+ *             largest this entry point is specified for); more is refused with SG_ERR_ARG and a message in
+ *             sg_last_error -- use sg_reduce_stats, or reduce in pieces and combine
+ *   device    the CURRENT device of the calling thread (there is no handle to name one); stats / agg_out live there
+ *   first call on each device: resolves the address of the built-in array on that device (cudaGetSymbolAddress).
+ *             Make that first call during set-up, before any stream capture is begun.
+ *   sharing   every call on a device uses the SAME array, on any stream and from any thread.  Each call overwrites
+ *             the rows it later reads, so nothing has to be cleared between calls and stale rows of an earlier,
+ *             larger call are never read; but two calls that can overlap on the GPU (different streams without an
+ *             event between them, or two host threads) race on it and give garbage.  Keep them on one stream or
+ *             order them yourself. */
+#define SG_REDUCE_STATIC_MAX_BLOCKS 592
+#define SG_REDUCE_STATIC_MAX_EPISODES 16777216
+int sg_reduce_stats_static(const double *stats, int64_t n_episodes, int64_t capacity, double *agg_out, void *stream);
+
 int64_t sg_num_episodes(sg_handle h);
 /* Kernels launched through this handle since sg_create (bench.py's gpu_launches). */
 int64_t sg_launch_count(sg_handle h);

@@ -27,6 +27,7 @@ STAT_COLS = ['rows', 'sum_bg', 'min_bg', 'max_bg', 'sum_lbgi', 'sum_hbgi', 'sum_
 CTRL_ACTIONS, CTRL_BB, CTRL_PID, CTRL_RANDOM = 0, 1, 2, 3
 FLAG_CARRY_H, FLAG_FMA, FLAG_FP32 = 1, 2, 8
 STATUS_STREAM_EXHAUSTED = -5
+REDUCE_STATIC_MAX_EPISODES = 16777216     # SG_REDUCE_STATIC_MAX_EPISODES
 
 # every symbol include/simglucose_b200.h declares
 SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_hardware', 'sg_load_params',
@@ -35,7 +36,7 @@ SYMBOLS = ['sg_version', 'sg_last_error', 'sg_create', 'sg_destroy', 'sg_set_har
            'sg_step_meals', 'sg_rebind_streams', 'sg_set_t0', 'sg_set_step_cap', 'sg_set_coherence', 'sg_set_sort_mode', 'sg_get_launch_order',
            'sg_reset_masked', 'sg_patient_step', 'sg_model', 'sg_pump',
            'sg_risk_index', 'sg_risk_window', 'sg_cgm_measure', 'sg_get_episode_state', 'sg_set_episode_state', 'sg_math_probe',
-           'sg_report_stats', 'sg_cvga_zones',
+           'sg_report_stats', 'sg_cvga_zones', 'sg_reduce_stats_static',
            'sg_gen_noise', 'sg_gen_scenarios', 'sg_gen_perturbed_params', 'sg_gen_uniform', 'sg_probe_dfma',
            'sg_gen_noise_keyed', 'sg_gen_scenarios_keyed', 'sg_gen_episode_starts', 'sg_vec_finish', 'sg_vec_restart',
            'sg_gen_noise_listed', 'sg_gen_scenarios_listed']
@@ -95,6 +96,7 @@ def load():
     L.sg_get_stats.argtypes = [vp, dp, vp]
     L.sg_get_status.argtypes = [vp, ip, vp]
     L.sg_reduce_stats.argtypes = [vp, dp, vp]
+    L.sg_reduce_stats_static.argtypes = [dp, C.c_int64, C.c_int64, dp, vp]
     L.sg_num_episodes.argtypes = [vp]
     L.sg_num_episodes.restype = C.c_int64
     L.sg_launch_count.argtypes = [vp]

@@ -32,6 +32,7 @@ UNITS = [
     ('sg_generators.o', 'sg_generators.cu', ['-fmad=true']),
     ('sg_coherence.o', 'sg_coherence.cu', ['-fmad=false']),
     ('sg_report.o', 'sg_report.cu', ['-fmad=false']),
+    ('sg_noalloc.o', 'sg_noalloc.cu', ['-fmad=false']),
     ('sg_capi.o', 'sg_capi.cu', ['-fmad=false']),
 ]
 

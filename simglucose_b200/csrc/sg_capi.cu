@@ -29,6 +29,11 @@ int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
 
 }  // namespace
 
+// For the entry points that live in other source files (sg_noalloc.cu): the same per-thread text sg_last_error returns.
+namespace sgk {
+void set_last_error(const char *what, cudaError_t ce) { fail(0, what, ce); }
+}
+
 struct sg_context {
     int device = 0;
     int64_t cap = 0, n = 0;
