@@ -325,6 +325,7 @@ class ShardRunner:
         self.engines = [BatchEngine(self.capacity, device=device, **engine_kw) for _ in range(max(1, int(slots)))]
         self.streams = [torch.cuda.Stream(device=self.device) for _ in self.engines]
         self._trace_dev = self._trace_sel = None
+        self._trace_shape = (0, 0)
 
     def run(self, shards, n_steps, controller='bb', ctrl=None, stats_out=None, traces_out=None,
             trace_cols=('BG', 'CGM', 'CHO', 'insulin')):
@@ -342,12 +343,19 @@ class ShardRunner:
         two-stream pipeline, profiles/r02_i_*.)"""
         shards = list(shards)
         cols = [_capi.TRACE_COLS.index(c) for c in trace_cols]
-        if traces_out is not None and self._trace_dev is None:
-            self._trace_dev = [torch.empty(n_steps, _capi.NTRACE, self.capacity, dtype=torch.float64, device=self.device)
-                               for _ in self.engines]
-            self._trace_sel = [torch.empty(n_steps, len(cols), self.capacity, dtype=torch.float64, device=self.device)
-                               for _ in self.engines]
-            self._cols = torch.tensor(cols, dtype=torch.int64, device=self.device)
+        if traces_out is not None:
+            # staging buffers are kept between calls and only ever grow; the column selection belongs to THIS call
+            need = (int(n_steps), len(cols))
+            if self._trace_dev is None or self._trace_shape[0] < need[0] or self._trace_shape[1] < need[1]:
+                have = self._trace_shape if self._trace_dev is not None else (0, 0)
+                self._trace_shape = (max(need[0], have[0]), max(need[1], have[1]))
+                self._trace_dev = [torch.empty(self._trace_shape[0], _capi.NTRACE, self.capacity, dtype=torch.float64,
+                                               device=self.device) for _ in self.engines]
+                self._trace_sel = [torch.empty(self._trace_shape[0], self._trace_shape[1], self.capacity,
+                                               dtype=torch.float64, device=self.device) for _ in self.engines]
+            if getattr(self, '_cols_key', None) != tuple(cols):
+                self._cols = torch.tensor(cols, dtype=torch.int64, device=self.device)
+                self._cols_key = tuple(cols)
         if stats_out is None:
             stats_out = [torch.empty(_capi.NSTAT, int(torch.as_tensor(s['patient_row']).numel()),
                                      dtype=torch.float64).pin_memory() for s in shards]

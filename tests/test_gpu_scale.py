@@ -222,6 +222,14 @@ def test_run_shards_streams_host_population_identically():
     tr_out = [torch.empty(n_steps, len(cols), hi - lo, dtype=torch.float64).pin_memory() for lo, hi in zip(cuts[:-1], cuts[1:])]
     stats2, agg2 = runner.run(shards, n_steps, controller='bb', traces_out=tr_out, trace_cols=cols)
     torch.cuda.synchronize()
+    # the same runner asked for OTHER columns (same count, then more): the selection belongs to each call
+    for cols2 in (('Risk', 'BG', 'LBGI', 'HBGI'), ('BG', 'CGM', 'CHO', 'insulin', 'reward', 'done')):
+        tr2 = [torch.empty(n_steps, len(cols2), hi - lo, dtype=torch.float64).pin_memory()
+               for lo, hi in zip(cuts[:-1], cuts[1:])]
+        runner.run(shards, n_steps, controller='bb', traces_out=tr2, trace_cols=cols2)
+        torch.cuda.synchronize()
+        want2 = trace[:, [_capi.TRACE_COLS.index(c) for c in cols2], :].cpu()
+        assert torch.equal(torch.nan_to_num(torch.cat(tr2, dim=2)), torch.nan_to_num(want2)), cols2
     runner.close()
     assert torch.equal(torch.cat(tr_out, dim=2), want_tr)
     assert torch.equal(torch.cat(stats2, dim=1), want)
