@@ -338,8 +338,12 @@ class T1DSimVecEnv(object):
         per-environment resets happen inside a rollout."""
         if self.steps is None:
             raise RuntimeError('call reset() first')
-        if self.steps + n_steps > self.horizon_steps:
-            raise RuntimeError('rollout past the episode horizon')
+        # with auto_reset the environments restarted one by one: what bounds a rollout is the OLDEST running episode
+        # (its noise stream ends at the horizon), not the env-steps taken since reset() -- one device read per rollout
+        oldest = int(self.episode_steps.max()) if self.auto_reset else self.steps
+        if oldest + n_steps > self.horizon_steps:
+            raise RuntimeError('rollout past the episode horizon (oldest episode at env-step %d of %d, %d more asked)'
+                               % (oldest, self.horizon_steps, n_steps))
         if controller == 'bb' and ctrl is None and ctrl_rows is None:
             q = torch.from_numpy(P.quest_table()).to(self.device)[self.patient_row.long()]
             tbl = P.cohort_table()[0]

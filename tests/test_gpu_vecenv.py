@@ -105,6 +105,14 @@ def test_device_seeded_vector_env_properties():
     st = a.statistics(reduce=False).cpu().numpy()
     assert np.array_equal(st[0], a.episode_steps.cpu().numpy() + 1)            # rows of the CURRENT episodes
     assert n_done > 0 and int(a.episodes_started.max()) > 2                     # environments that ended on `done`
+    # a fused rollout after per-environment restarts is bounded by the OLDEST running episode, not by the env-steps
+    # taken since reset() (horizon + 5 by now)
+    oldest = int(a.episode_steps.max())
+    assert a.steps == horizon + 5 and oldest < horizon
+    with pytest.raises(RuntimeError, match='past the episode horizon'):
+        a.rollout(horizon - oldest + 1, controller='bb')
+    a.rollout(horizon - oldest, controller='bb')
+    assert int((a.engine.status() != 1).sum()) == 0                            # no stream ran out
     a.close(); b.close()
 
 
