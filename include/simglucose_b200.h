@@ -62,8 +62,11 @@ typedef enum {
     SG_CTRL_PID = 2,         /* PIDController.policy, controller/pid_ctrller.py:17-36; ctrl = P, I, D, target */
     SG_CTRL_RANDOM = 3       /* Action(basal ~ U(lo, hi), bolus 0): what gym's action_space.sample() feeds
                                 T1DSimEnv._step (envs/simglucose_gym_env.py:41-46, 78-81), drawn inside the kernel from
-                                Philox keyed by (seed, global episode index, env-step index);
-                                ctrl = lo, hi, seed, global index of episode 0 (whole numbers below 2^53) */
+                                Philox keyed by (seed, global episode index, env-step index counted from the last
+                                sg_reset -- sg_reset_masked does not restart it, so environments that restart one
+                                by one keep drawing fresh actions);
+                                ctrl = lo, hi, seed, global index of episode 0 (whole numbers in [0, 2^53); anything
+                                else is refused) */
 } sg_controller;
 #define SG_NCTRL 4
 

@@ -68,12 +68,13 @@ struct sg_context {
     int32_t steps_since_sort = 0;
     bool perm_valid = false;
     int32_t *perm = nullptr, *sort_keys = nullptr, *sort_hist = nullptr;
-    int32_t sort_n_keys = 0;
+    int32_t sort_n_keys = 0;           // keys of the current (segment, sample_time): what the sort kernels are told
+    int32_t sort_hist_keys = 0;        // keys sort_hist was allocated for (>= sort_n_keys)
     int32_t sort_mode = 0;             // sg_set_sort_mode: 0 by next meal event, 1 adaptive (recent DOPRI5 steps)
     double *sort_prev_steps = nullptr;
     // episodes with positions of their own (sg_reset_masked): the host-side stream length check no longer applies
     bool per_episode_positions = false;
-    int64_t steps_total = 0;           // env-steps launched since sg_create (Philox counter of SG_CTRL_RANDOM)
+    int64_t steps_total = 0;           // env-steps launched since the last sg_reset (Philox counter of SG_CTRL_RANDOM)
 };
 
 namespace {
@@ -107,6 +108,35 @@ sgk::EpisodeArgs base_args(const sg_context *h)
 }
 
 bool use_fma(const sg_context *h) { return (h->flags & SG_FLAG_FMA) != 0; }
+
+// Buffers of the launch-order sort for a segment of `segment_steps` env-steps at a sensor period of `st` minutes.  The
+// key space grows with segment_steps * st, so both sg_set_coherence and a later sg_set_hardware (another sample_time)
+// come through here; h->sort_n_keys always matches what the next sort will be told.
+int size_sort_buffers(sg_context *h, int32_t segment_steps, int32_t st, const char *who)
+{
+    static thread_local char msg[160];
+    const int64_t window = (int64_t)segment_steps * st;
+    if (window > 4096) {
+        snprintf(msg, sizeof msg, "%s: at most 4096 minutes between two sorts (segment of %d env-steps x %d min)", who,
+                 (int)segment_steps, (int)st);
+        return fail(SG_ERR_ARG, msg);
+    }
+    const int32_t n_keys = sgc::key_count((int32_t)window);
+    if (!h->perm) {
+        cudaError_t ce = cudaMalloc(&h->perm, sizeof(int32_t) * h->cap);
+        if (ce == cudaSuccess) ce = cudaMalloc(&h->sort_keys, sizeof(int32_t) * h->cap);
+        if (ce != cudaSuccess) { snprintf(msg, sizeof msg, "%s: cudaMalloc", who); return fail(SG_ERR_NOMEM, msg, ce); }
+    }
+    if (n_keys > h->sort_hist_keys) {
+        cudaFree(h->sort_hist);
+        h->sort_hist = nullptr; h->sort_hist_keys = 0; h->sort_n_keys = 0;
+        cudaError_t ce = cudaMalloc(&h->sort_hist, sizeof(int32_t) * n_keys);
+        if (ce != cudaSuccess) { snprintf(msg, sizeof msg, "%s: cudaMalloc", who); return fail(SG_ERR_NOMEM, msg, ce); }
+        h->sort_hist_keys = n_keys;
+    }
+    h->sort_n_keys = n_keys;
+    return SG_OK;
+}
 
 }  // namespace
 
@@ -162,6 +192,13 @@ int sg_set_hardware(sg_handle h, const sg_hardware *hw)
     if (!h || !hw) return fail(SG_ERR_ARG, "sg_set_hardware: null argument");
     if (hw->sample_time < 1 || !(hw->pump[2] > 0.0) || !(hw->pump[5] > 0.0))
         return fail(SG_ERR_ARG, "sg_set_hardware: sample_time >= 1 and pump increments > 0 required");
+    if (h->coherence_steps > 0 && hw->sample_time != h->hw.st) {
+        // the sort keys count minutes: another sensor period is another key space (refused if it no longer fits)
+        DeviceGuard g(h->device);
+        const int rc = size_sort_buffers(h, h->coherence_steps, hw->sample_time, "sg_set_hardware (coherent launch order on)");
+        if (rc != SG_OK) return rc;
+        h->perm_valid = false;
+    }
     h->hw.st = hw->sample_time;
     h->hw.smin = hw->sensor_min; h->hw.smax = hw->sensor_max;
     memcpy(h->hw.pump, hw->pump, sizeof h->hw.pump);
@@ -203,6 +240,7 @@ int sg_reset(sg_handle h, int64_t n_episodes, const int32_t *patient_row, const 
     h->meal_minute = meal_minute; h->meal_grams = meal_grams; h->max_meals = max_meals;
     h->noise = noise; h->n_noise = n_noise;
     h->steps_done = 0;
+    h->steps_total = 0;            // SG_CTRL_RANDOM counts env-steps from here: a reused handle draws what a fresh one does
     h->perm_valid = false;
     h->per_episode_positions = false;
     sgk::EpisodeArgs a = base_args(h);
@@ -227,6 +265,8 @@ static int sort_episodes(sg_handle h, cudaStream_t stream)
     sa.steps_between = h->coherence_steps; sa.st = h->hw.st;
     sa.window = h->coherence_steps * h->hw.st;
     sa.n_keys = h->sort_n_keys;
+    if (!h->sort_hist || sgc::key_count(sa.window) != h->sort_n_keys || h->sort_n_keys > h->sort_hist_keys)
+        return fail(SG_ERR_STATE, "launch-order sort: key space does not match the allocated histogram");
     sa.keys = h->sort_keys; sa.hist = h->sort_hist; sa.perm = h->perm;
     cudaError_t ce = sgc::launch_sort(sa, stream);
     if (ce != cudaSuccess) return fail(SG_ERR_CUDA, "sg_set_coherence: sort launch", ce);
@@ -305,6 +345,13 @@ int sg_run(sg_handle h, int32_t controller, const double *ctrl_host, const doubl
     if (controller < SG_CTRL_ACTIONS || controller > SG_CTRL_RANDOM) return fail(SG_ERR_ARG, "sg_run: unknown controller");
     if (controller == SG_CTRL_ACTIONS && !actions) return fail(SG_ERR_ARG, "sg_run: actions required");
     if (controller != SG_CTRL_ACTIONS && !ctrl_host && !ctrl_rows) return fail(SG_ERR_ARG, "sg_run: controller constants required");
+    if (controller == SG_CTRL_RANDOM) {
+        // seed and first global index travel as doubles and are cast to uint64 in the kernel: whole numbers in [0, 2^53)
+        if (!ctrl_host) return fail(SG_ERR_ARG, "sg_run: SG_CTRL_RANDOM takes its constants from ctrl_host");
+        for (int i = 2; i < 4; i++)
+            if (!(ctrl_host[i] >= 0.0 && ctrl_host[i] < 9007199254740992.0 && ctrl_host[i] == (double)(uint64_t)ctrl_host[i]))
+                return fail(SG_ERR_ARG, "sg_run: SG_CTRL_RANDOM seed and first episode index must be whole numbers in [0, 2^53)");
+    }
     return run_impl(h, controller, ctrl_host, ctrl_rows, actions, actions ? actions + h->n : nullptr, 2 * h->n,
                     n_steps, trace, counters, stream, "sg_run");
 }
@@ -361,21 +408,8 @@ int sg_set_coherence(sg_handle h, int32_t segment_steps)
     if (segment_steps > 0 && !h->have_hw) return fail(SG_ERR_STATE, "sg_set_coherence: call sg_set_hardware first");
     DeviceGuard g(h->device);
     if (segment_steps > 0) {
-        const int64_t window = (int64_t)segment_steps * h->hw.st;
-        if (window > 4096) return fail(SG_ERR_ARG, "sg_set_coherence: at most 4096 minutes between two sorts");
-        const int32_t n_keys = sgc::key_count((int32_t)window);
-        if (!h->perm) {
-            cudaError_t ce = cudaMalloc(&h->perm, sizeof(int32_t) * h->cap);
-            if (ce == cudaSuccess) ce = cudaMalloc(&h->sort_keys, sizeof(int32_t) * h->cap);
-            if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_coherence: cudaMalloc", ce);
-        }
-        if (n_keys > h->sort_n_keys) {
-            cudaFree(h->sort_hist);
-            h->sort_hist = nullptr; h->sort_n_keys = 0;
-            cudaError_t ce = cudaMalloc(&h->sort_hist, sizeof(int32_t) * n_keys);
-            if (ce != cudaSuccess) return fail(SG_ERR_NOMEM, "sg_set_coherence: cudaMalloc", ce);
-        }
-        h->sort_n_keys = n_keys;
+        const int rc = size_sort_buffers(h, segment_steps, h->hw.st, "sg_set_coherence");
+        if (rc != SG_OK) return rc;
     }
     h->coherence_steps = segment_steps;
     h->perm_valid = false;

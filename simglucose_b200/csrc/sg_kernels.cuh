@@ -72,7 +72,7 @@ struct EpisodeArgs {
     int32_t carry_h;
     // run
     int32_t controller;
-    int64_t step0;             // env-steps this handle has launched so far (SG_CTRL_RANDOM: Philox counter)
+    int64_t step0;             // env-steps this handle has launched since sg_reset (SG_CTRL_RANDOM: Philox counter)
     double ctrl[NCTRL];
     const double *ctrl_rows;   // [NCTRL][n] or null
     const double *act_basal;   // step k of episode e at act_basal[k * act_stride + e]

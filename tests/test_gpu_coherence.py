@@ -143,6 +143,47 @@ def test_coherent_lockstep_steps_equal_fused_run():
     _same(want, got)
 
 
+def test_sensor_switch_after_set_coherence_resizes_the_sort():
+    """The sort keys count MINUTES ahead, so their number grows with segment_steps * sample_time.  Switching the sensor
+    (Dexcom, 3 min -> GuardianRT, 5 min) after set_coherence used to leave the histogram sized for the old period and
+    the sort wrote past it.  Now sg_set_hardware re-sizes it (or refuses a segment that no longer fits 4096 minutes),
+    and the results stay those of the unsorted order."""
+    import torch
+    from simglucose_b200 import _capi, params as P, streams as S
+    from simglucose_b200.engine import BatchEngine
+    E, n_steps = 9000, 72                                  # 6 h at 5-minute env-steps, from 06:00
+    dev = torch.device('cuda', 0)
+    rows = (torch.arange(E, device=dev, dtype=torch.int64) % 30).to(torch.int32)
+    noise = S.device_noise(E, n_steps + 2, 'GuardianRT', seed=23, group_size=1, device=dev)
+    mm, mg = S.device_scenarios(E, n_steps * 5, start_minute=360, seed=23, group_size=1, device=dev)
+
+    def run(eng):
+        eng.reset(rows, noise, mm, mg, row0=False)
+        out = eng.run(n_steps, controller='pid', ctrl=(1e-3, 1e-5, 1e-3, 140.0), trace=True, counters=True)
+        return _snapshot(eng, out)
+    plain = BatchEngine(E, sensor='GuardianRT')
+    base = run(plain)
+    plain.close()
+    eng = BatchEngine(E, coherence=20)                      # Dexcom: 60-minute window, 7,809 keys
+    eng.set_hardware('GuardianRT')                          # 100-minute window, 12,929 keys
+    got = run(eng)
+    perm = eng.launch_order().cpu().numpy()
+    _same(base, got)
+    assert np.array_equal(np.sort(perm), np.arange(E))
+    # a per-step sort through the shared-memory histogram (small key space) after the same switch
+    eng.set_coherence(1, adaptive=True)                     # GuardianRT: 5-minute window, 6 x 128 + 1 keys
+    eng.set_hardware('Navigator')                           # 1-minute sensor: 2 x 128 + 1 keys
+    eng.set_hardware('GuardianRT')
+    _same(base, run(eng))
+    # a segment that fits at 3 minutes but not at 5 is refused, and the handle keeps its sensor
+    eng.set_hardware('Dexcom')
+    eng.set_coherence(1000)                                 # 3,000 minutes
+    with pytest.raises(_capi.SgError, match='4096 minutes'):
+        eng.set_hardware('GuardianRT')                      # 5,000 minutes
+    assert eng.sample_time == 3
+    eng.close()
+
+
 def test_masked_reset_restarts_only_the_masked_episodes():
     import torch
     from simglucose_b200 import streams as S
@@ -217,6 +258,16 @@ def test_random_action_controller():
     d = BatchEngine(E)
     d.reset(rows, noise, mm, mg, row0=False)
     _same(sa, _snapshot(d, dict(trace=d.run(n_steps, controller='actions', actions=acts, trace=True)['trace'])))
+    # a REUSED handle (second wave of a sweep, a ShardRunner slot) draws what a fresh one does: the env-step index of
+    # the Philox counter restarts at sg_reset, whatever ran through the handle before (here: a bb warm-up and a run)
+    d.reset(rows, noise, mm, mg, row0=False)
+    d.run(7, controller='bb', ctrl=(140.0, 10.0, 30.0), trace=False)
+    d.reset(rows, noise, mm, mg, row0=False)
+    _same(sa, _snapshot(d, dict(trace=d.run(n_steps, controller='random', ctrl=(0.0, 0.05, 11.0, 1000.0), trace=True)['trace'])))
+    # seed and offset are cast to unsigned integers in the kernel: negative or fractional values are refused
+    for bad in ((0.0, 0.05, -1.0, 0.0), (0.0, 0.05, 11.5, 0.0), (0.0, 0.05, 11.0, -4.0), (0.0, 0.05, float('nan'), 0.0)):
+        with pytest.raises(_capi.SgError, match='whole numbers'):
+            d.run(1, controller='random', ctrl=bad, trace=False)
     for e in (a, b, c, d):
         e.close()
 
