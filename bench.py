@@ -95,6 +95,9 @@ def parse():
     ap.add_argument('--episodes', type=int, default=16777216, help='--config 3: total episodes over all ranks')
     ap.add_argument('--sweep-days', type=int, default=7, help='--config 3: simulated days')
     ap.add_argument('--wave', type=int, default=2097152, help='--config 3: episodes resident per GPU at a time')
+    ap.add_argument('--c3-episodes', type=int, default=16777216,
+                    help='episodes of the configs[3] entry of the default line (its stated size by default)')
+    ap.add_argument('--c3-days', type=int, default=7, help='simulated days of the configs[3] entry of the default line')
     return ap.parse_args()
 
 
@@ -593,8 +596,17 @@ def main():
     rows_h = rows.cpu().numpy()
     ctrl_rows = controller_rows_device(rows)
     # inputs resident in HBM before the timed region
+    # (generated on device, once, outside the timed region; SURVEY.md 8d asks for its cost to be reported: the first
+    # call also pays the library's module load, the second is the generation itself)
+    S.device_noise(30, 8, 'Dexcom', seed=1, device=dev)
+    torch.cuda.synchronize(dev)
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
     noise = S.device_noise(E, n_steps + 2, 'Dexcom', seed=1, episode_offset=ep0, group_size=30, device=dev)
     mm, mg = S.device_scenarios(E, n_min, start_minute=0, seed=1, episode_offset=ep0, group_size=30, device=dev)
+    g1.record()
+    torch.cuda.synchronize(dev)
+    stream_generation_s = g0.elapsed_time(g1) * 1e-3
     eng = BatchEngine(E, device=local, carry_h=args.carry_h, fma=args.fma, fp32=args.fp32, coherence=coherence,
                       adaptive_sort=args.adaptive_sort)
     agg = torch.zeros(_capi.NSTAT, dtype=torch.float64, device=dev)
@@ -771,24 +783,32 @@ def main():
     del noise, mm, mg, eng
     torch.cuda.empty_cache()
 
-    # ---- the other BASELINE.json configurations: [2] and [4] at their stated sizes, [3] reduced (full size: --config 3,
-    # profiles/), [0] through the single-environment facade ----
+    # ---- the other BASELINE.json configurations: [2], [3] and [4] at their stated sizes, [0] through the
+    # single-environment facade ----
     configs = None
     if not args.no_configs:
         configs = {}
         # configs[3] is the multi-GPU configuration: a reduced population (262,144 episodes x 1 day) sharded over ALL
         # ranks with the statistics all-reduce inside its timed region, at every N
+        # at its STATED size by default (16,777,216 episodes x 7 days: 97 / 48 / 24 / 12 s on 1 / 2 / 4 / 8 GPUs), after a
+        # small warm-up; --c3-episodes / --c3-days shrink it for quick runs
         coh3 = 40 if args.coherence < 0 else args.coherence
+        c3_total, c3_days = int(args.c3_episodes), int(args.c3_days)
         config3(local, rank, world, 262144, 1, 2097152, coh3)                      # warm-up
-        sec3, agg3, failed3, launches3, gen3, _ = config3(local, rank, world, 262144, 1, 2097152, coh3)
+        sec3, agg3, failed3, launches3, gen3, _ = config3(local, rank, world, c3_total, c3_days, args.wave, coh3)
         t3 = torch.tensor([sec3], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t3, op=dist.ReduceOp.MAX)
         configs['configs[3]'] = {
-            'config': 'configs[3] reduced: 262,144 episodes with +-10 %% perturbed parameters x 1 day, BBController, '
-                      'independent streams, sharded over %d GPU(s) (shard_range), distributed.allreduce_stats inside '
-                      'the timed region; full size (16,777,216 x 7 days): bench.py --config 3, profiles/' % world,
-            'value': 262144 * 1440 / float(t3.item()), 'unit': METRIC, 'seconds': float(t3.item()), 'n_gpus': world,
+            'config': 'configs[3]%s: %d episodes with +-10 %% perturbed parameters (Philox seed 1234, keyed by global '
+                      'episode index) x %d day(s), BBController (nominal basal by name), independent streams, sharded '
+                      'over %d GPU(s) (shard_range) in resident waves of %d, distributed.allreduce_stats inside the timed '
+                      'region; the integer entries and extrema of population_vector_hex do not depend on the number of '
+                      'GPUs (tools/check_scale_vectors.py)'
+                      % (' at its stated size' if (c3_total, c3_days) == (16777216, 7) else ' reduced', c3_total, c3_days,
+                         world, args.wave),
+            'episodes': c3_total, 'days': c3_days,
+            'value': c3_total * 1440.0 * c3_days / float(t3.item()), 'unit': METRIC, 'seconds': float(t3.item()), 'n_gpus': world,
             'coherence_steps': coh3, 'solver_failures': failed3, 'library_launches_rank0': launches3,
             'includes': 'parameter / stream generation on device (%.3f s on rank 0), reset, episode kernel, reduction, '
                         'all-reduce' % gen3,
@@ -823,8 +843,15 @@ def main():
                 'config': {'workload': 'configs[1] cohort: 30 virtual patients x %d seed groups per GPU x %d-day '
                                        'RandomScenario, BBController, Dexcom, Insulet' % (args.groups, args.days),
                            'episodes_per_gpu': E, 'minutes_per_episode': n_min, 'arithmetic': ('fp32 integrator (optional mode, looser bound)' if args.fp32 else
-                                          'fma' if args.fma else 'strict (no FMA contraction)'),
+                                          'fma' if args.fma else
+                                          'strict part: patient model RHS and Runge-Kutta stage sums, every operation rounded '
+                                          'separately in the reference\'s order (no FMA contraction); <= 2 ulp part: scaled norms '
+                                          'of HINIT and of the error estimate (reciprocal products), step-size controller (exp of '
+                                          'log), tanh bracket of the gastric-emptying law, risk index'),
                            'carry_h': bool(args.carry_h), 'coherence_steps': coherence,
+                           'stream_generation_s_rank0': stream_generation_s,
+                           'stream_generation': 'CGM noise and meal schedules of the whole population, generated on device '
+                                                'once before the timed region (not part of value / e2e)',
                            'parallelism': 'episodes sharded, dp%d; distributed.allreduce_stats (NCCL) once per step inside '
                                           'the timed region' % world,
                            'l2': 'inputs (%.1f GB noise per GPU) larger than L2' % ((n_steps + 2) * E * 8 / 1e9)},

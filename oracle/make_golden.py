@@ -95,6 +95,50 @@ def g_late_start(pool):
     _save('late_start', pool.map(_episode, jobs))
 
 
+PERTURB_SEED, PERTURB_AMPLITUDE = 1234, 0.1        # bench.py config3() / BASELINE.json configs[3]
+
+
+def _perturbed_jobs(indices, n_steps):
+    """Episodes of the configs[3] population by GLOBAL index g: patient row g % 30, the parameter row the device
+    generator draws for g (oracle/philox_host.py restates sg_gen_perturbed_params), RandomScenario / CGMSensor seeded
+    with g (independent streams per episode), BBController (nominal basal, CR, CF by patient name), CSV x0."""
+    import oracle as O
+    import philox_host as PH
+    names = H.patient_names()
+    jobs, rows = [], []
+    for g in indices:
+        nominal, _ = O.patient_params(g % 30)
+        row = PH.perturbed_row(nominal, PERTURB_AMPLITUDE, PERTURB_SEED, g)
+        rows.append(row)
+        jobs.append((names[g % 30], n_steps, dict(controller=('bb', 140.0), scenario=('random', g), start_hour=0,
+                                                  sensor_seed=g, params_override=dict(zip(O.HOT_PARAMS, row)))))
+    return jobs, rows
+
+
+def _perturbed(pool, name, indices, n_steps):
+    jobs, rows = _perturbed_jobs(indices, n_steps)
+    recs = pool.map(_episode, jobs)
+    for r, g, row in zip(recs, indices, rows):
+        r['global_index'] = np.int64(g)
+        r['params'] = row
+    _save(name, recs, perturb_seed=np.int64(PERTURB_SEED), perturb_amplitude=np.float64(PERTURB_AMPLITUDE))
+
+
+def g_perturbed(pool):
+    """BASELINE.json configs[3] subset: the UNMODIFIED reference run on +-10 % perturbed parameter rows -- global
+    episodes 0..59 x 1 day (every patient twice; a dozen of them dip below 50 mg/dL on the first day)."""
+    _perturbed(pool, 'perturbed_1day', list(range(60)), 480)
+
+
+# 7 days: two rows that stay physiological (7, 33) and three that the reference drives to BG ~ 0, where x3, x4, x12
+# ride the (x >= 0) * dxdt masks of t1dpatient.py:167, 173, 202 (found by scanning episodes 0..399 with the C oracle)
+PERTURBED_WEEK = [7, 22, 33, 57, 297]
+
+
+def g_perturbed_week(pool):
+    _perturbed(pool, 'perturbed_7day', PERTURBED_WEEK, 7 * 480)
+
+
 def g_cohort_bb(pool):
     """BASELINE.json configs[1]: all 30 patients x 3 days, RandomScenario seed 1, BBController."""
     names = H.patient_names()
@@ -249,7 +293,8 @@ def g_generator_samples(pool):
 
 GROUPS = dict(golden_config=g_golden_config, custom=g_custom, cohort_bb=g_cohort_bb, cohort_pid=g_cohort_pid,
               open_loop=g_open_loop, hardware=g_hardware, gym=g_gym, noise=g_noise, report=g_report,
-              generator_samples=g_generator_samples, late_start=g_late_start)
+              generator_samples=g_generator_samples, late_start=g_late_start, perturbed=g_perturbed,
+              perturbed_week=g_perturbed_week)
 
 if __name__ == '__main__':
     groups = sys.argv[1:] or list(GROUPS)

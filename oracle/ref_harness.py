@@ -40,15 +40,22 @@ def reference_available():
     return os.path.isdir(os.path.join(REFERENCE_ROOT, 'simglucose'))
 
 
-def make_patient(name, **kw):
+def make_patient(name, params_override=None, **kw):
     """T1DPatient.withName (patient/t1dpatient.py:57-68) with the ndarray
-    init_state shim."""
+    init_state shim.  params_override: {column: value} written into the parameter Series before the
+    patient is built -- T1DPatient.__init__ (t1dpatient.py:22-42) takes any Series; the Name (what
+    BBController looks u2ss / BW / CR / CF up by, basal_bolus_ctrller.py:52-64) and the x0 columns stay
+    those of the CSV row."""
     _activate()
     import pandas as pd
     from simglucose.patient.t1dpatient import T1DPatient, PATIENT_PARA_FILE
     csv = pd.read_csv(PATIENT_PARA_FILE)
-    params = csv.loc[csv.Name == name].squeeze()
+    params = csv.loc[csv.Name == name].squeeze().copy()
     x0 = params.iloc[2:15].to_numpy(float).copy()
+    if params_override:
+        for col, val in params_override.items():
+            assert col in params.index and not col.startswith('x0_'), col
+            params[col] = float(val)
     return T1DPatient(params, init_state=x0, **kw)
 
 
@@ -74,7 +81,7 @@ def noise_stream(sensor_name, seed, n):
 
 def run_episode(patient_name, n_steps, controller=('bb', 140.0), scenario=('random', 1),
                 start_hour=0, sensor_name='Dexcom', sensor_seed=1, pump_name='Insulet',
-                actions=None, random_init_bg=False, patient_seed=None, t0=0):
+                actions=None, random_init_bg=False, patient_seed=None, t0=0, params_override=None):
     """Run the reference closed loop for n_steps env-steps exactly as
     SimObj.simulate does (simulation/sim_engine.py:29-39), recording inputs and
     outputs.
@@ -94,7 +101,8 @@ def run_episode(patient_name, n_steps, controller=('bb', 140.0), scenario=('rand
     from simglucose.simulation.scenario import CustomScenario
 
     start_time = datetime(2018, 1, 1, start_hour, 0, 0)
-    patient = make_patient(patient_name, random_init_bg=random_init_bg, seed=patient_seed, t0=t0)
+    patient = make_patient(patient_name, params_override=params_override, random_init_bg=random_init_bg,
+                           seed=patient_seed, t0=t0)
     sensor = CGMSensor.withName(sensor_name, seed=sensor_seed)
     pump = InsulinPump.withName(pump_name)
     if scenario[0] == 'random':

@@ -375,8 +375,11 @@ int sgo_run_episode(const sgo_config *cfg, const double *p, const double *x0, in
         /* controller.policy(obs, reward, done, **info) */
         double a_basal, a_bolus;
         if (cfg->controller == SGO_CTRL_BB) {
-            /* basal_bolus_ctrller.py:64-80; ctrl = target, CR, CF */
-            a_basal = p[SGO_u2ss] * p[SGO_BW] / 6000.0;
+            /* basal_bolus_ctrller.py:64-80; ctrl = target, CR, CF, basal.  The reference looks u2ss and BW up in the
+             * CSV by patient NAME (basal_bolus_ctrller.py:52-58), not in the patient object: a patient built on a
+             * perturbed parameter Series keeps the nominal basal.  ctrl[3] > 0 carries that nominal u2ss * BW / 6000;
+             * 0 = the episode's own row (the same number for the 30 CSV rows). */
+            a_basal = (cfg->ctrl[3] > 0.0) ? cfg->ctrl[3] : p[SGO_u2ss] * p[SGO_BW] / 6000.0;
             if (info_meal > 0) {
                 double corr = (obs > 150 ? 1.0 : 0.0) * (obs - cfg->ctrl[0]) / cfg->ctrl[2];
                 a_bolus = (info_meal * st) / cfg->ctrl[1] + corr;

@@ -33,6 +33,11 @@ def controller_of(d, i):
     row = int(d['patient_row'][i])
     if kind == 'bb':
         cr, cf = O.quest(row)
+        if 'params' in d.files:
+            # perturbed parameter rows: the reference's BBController still finds u2ss and BW by patient NAME
+            # (basal_bolus_ctrller.py:52-64), so the nominal basal travels with the controller constants
+            nominal, _ = O.patient_params(row)
+            return 'bb', (float(cp[0]), cr, cf, float(nominal[1] * nominal[0] / 6000.0))
         return 'bb', (float(cp[0]), cr, cf)
     if kind.startswith('pi'):
         return 'pid', tuple(float(v) for v in cp[:4])
@@ -48,6 +53,8 @@ def hardware_of(d, i):
 def oracle_episode(d, i, carry_h=0):
     row = int(d['patient_row'][i])
     p, _ = O.patient_params(row)
+    if 'params' in d.files:
+        p = d['params'][i]                      # the parameter Series the reference patient was built on
     kind, ctrl = controller_of(d, i)
     sn, pn = hardware_of(d, i)
     mm, mg = d['meal_minute'][i], d['meal_grams'][i]

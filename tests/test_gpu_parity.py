@@ -37,8 +37,9 @@ def _run_fixture(d, idx, carry_h=False, fma=False, counters=True):
         k, c = H.controller_of(d, i)
         assert k == kind and int(d['n_steps'][i]) == n_steps
         ctrl_rows[:len(c), j] = c
+    params = np.ascontiguousarray(d['params'][idx].T) if 'params' in d.files else None     # perturbed rows [32, E]
     row0 = eng.reset(d['patient_row'][idx], d['noise'][idx].T, d['meal_minute'][idx].T, d['meal_grams'][idx].T,
-                     x0=d['x0'][idx].T)
+                     x0=d['x0'][idx].T, params=params)
     actions = np.ascontiguousarray(d['actions'][idx].transpose(1, 2, 0)) if kind == 'actions' else None
     out = eng.run(n_steps, controller=kind, ctrl_rows=ctrl_rows, actions=actions, trace=True, counters=counters)
     tr = np.concatenate([row0.cpu().numpy()[None], out['trace'].cpu().numpy()], 0)   # [n_steps+1, NTRACE, E]
@@ -126,7 +127,41 @@ def test_cohort_bb_3day_all_30_patients():
     res = _run_fixture(d, range(30))
     _check_against_reference(d, range(30), res)
     same = (res['counters'][:, 0, :].T == d['dop_counters'][:, :, 1])
-    assert same.mean() >= 0.999, same.mean()
+    same_rej = (res['counters'][:, 1, :].T == d['dop_counters'][:, :, 3]) if res['counters'].shape[1] > 1 else same
+    # the count itself goes on record (pytest -s; profiles/r03_*): how many of the 129,600 patient-minutes take a
+    # different number of DOPRI5 steps / rejections than scipy did (norms and step controller are <= 2 ulp, not IEEE
+    # quotients: a decision can flip only when errsum lands within that of the threshold)
+    print('cohort_bb_3day: %d of %d patient-minutes differ from scipy in DOPRI5 steps, %d in rejections'
+          % (int((~same).sum()), same.size, int((~same_rej).sum())))
+    # measured on a B200 (profiles/r03_c_gpu_all.log): 0 of 129,600 differ, in steps and in rejections -- held to that
+    assert same.all() and same_rej.all(), (int((~same).sum()), int((~same_rej).sum()))
+
+
+@pytest.mark.parametrize('fixture', ['perturbed_1day', 'perturbed_7day'])
+def test_perturbed_parameter_rows_against_reference(fixture):
+    """BASELINE.json configs[3] anchored in the reference: episodes of the +-10 % perturbed population (global indices
+    0..59 for a day; five for a week, three of which collapse to BG ~ 0) simulated by the UNMODIFIED reference on the
+    perturbed parameter Series, against the CUDA path through params_soa + ctrl_rows[3] (the nominal basal the
+    reference's BBController finds by patient name, basal_bolus_ctrller.py:52-64).  Same bounds as every other
+    reference fixture.  And the device generator hands the simulator exactly the rows the fixture was recorded on."""
+    import torch
+    from simglucose_b200 import streams as S
+    d = H.load(fixture)
+    n = d['patient_row'].shape[0]
+    res = _run_fixture(d, range(n))
+    _check_against_reference(d, range(n), res)
+    same = (res['counters'][:, 0, :].T == d['dop_counters'][:, :, 1])
+    print('%s: %d of %d patient-minutes differ from scipy in their DOPRI5 step count' % (fixture, int((~same).sum()), same.size))
+    assert same.all(), int((~same).sum())          # measured: none (profiles/r03_c_gpu_all.log)
+    if fixture == 'perturbed_7day':
+        assert 2 <= int((np.nanmin(d['BG'], axis=1) < 1.0).sum()) < n      # collapsed and physiological rows both present
+    # sg_gen_perturbed_params at these global indices == the rows the reference patients were built on, bit for bit
+    for i in range(n):
+        g = int(d['global_index'][i])
+        row = torch.tensor([g % 30], dtype=torch.int32, device='cuda:0')
+        got = S.device_perturbed_params(row, amplitude=float(d['perturb_amplitude']), seed=int(d['perturb_seed']),
+                                        episode_offset=g)
+        assert np.array_equal(got.cpu().numpy()[:, 0], d['params'][i]), g
 
 
 def test_cohort_pid_1day():
